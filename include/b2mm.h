@@ -1,0 +1,159 @@
+/*
+ * b2mm.h — C ABI of the B200-native dense-GEMM hot path.
+ *
+ * This is the drop-in boundary for the operators the reference benchmark
+ * scripts reach on their timed paths.  The reference has no FFI of its own
+ * (it is pure Python over torch); each entry point below therefore names the
+ * torch call site it stands in for (paths relative to the reference repo).
+ *
+ * Conventions (all entry points)
+ *   - plain pointers and sizes only; device pointers unless stated otherwise;
+ *   - row-major, C = A * B, no alpha/beta, no transposes (what torch.matmul
+ *     does on contiguous 2-D/3-D inputs);
+ *   - asynchronous and ordered on `stream`; no host synchronisation inside,
+ *     so CUDA-event timing around a call measures the kernel;
+ *   - the library borrows pointers for the duration of the enqueued work and
+ *     never frees or reallocates caller memory;
+ *   - every function returns a b2mm_status; on failure a human-readable
+ *     message is available from b2mm_last_error() (thread local);
+ *   - there is no cuBLAS / CPU fallback: an unsupported shape is an error.
+ */
+#ifndef B2MM_H_
+#define B2MM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2MM_VERSION 100 /* major*10000 + minor*100 + patch */
+
+#if defined(__GNUC__)
+#define B2MM_API __attribute__((visibility("default")))
+#else
+#define B2MM_API
+#endif
+
+typedef enum b2mm_status {
+  B2MM_OK = 0,
+  B2MM_ERR_BAD_ARG = 1,     /* null pointer, negative size, unknown dtype        */
+  B2MM_ERR_UNSUPPORTED = 2, /* legal GEMM, but a shape/stride this build rejects  */
+  B2MM_ERR_CUDA = 3,        /* a CUDA runtime/driver call failed                  */
+  B2MM_ERR_NCCL = 4,        /* a NCCL call failed / libnccl could not be loaded   */
+  B2MM_ERR_WORKSPACE = 5    /* caller-supplied workspace too small                */
+} b2mm_status;
+
+typedef enum b2mm_dtype {
+  B2MM_BF16 = 0, /* torch.bfloat16: bf16 in, fp32 accumulate, bf16 out */
+  B2MM_FP16 = 1, /* torch.float16:  fp16 in, fp32 accumulate, fp16 out */
+  B2MM_FP32 = 2  /* torch.float32:  fp32 in/out, 3xTF32 split on tensor cores */
+} b2mm_dtype;
+
+/* CUDA stream handle, passed as an opaque pointer (cudaStream_t). */
+typedef void* b2mm_stream_t;
+
+/* Library version (B2MM_VERSION of the build). */
+B2MM_API int b2mm_version(void);
+
+/* Message for the last non-OK status returned on this thread ("" if none). */
+B2MM_API const char* b2mm_last_error(void);
+
+/* Number of kernels of THIS library launched by the calling process so far
+ * (all threads).  bench.py reports the delta over its timed region. */
+B2MM_API uint64_t b2mm_launch_count(void);
+
+/*
+ * Bytes of scratch b2mm_gemm needs for this problem (0 for bf16/fp16).
+ * fp32 needs room for the TF32 hi/lo split of both operands.
+ */
+B2MM_API size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype);
+
+/*
+ * C[b] = A[b] * B[b]  for b in [0, batch).
+ *
+ * Replaces torch.matmul(A, B) at matmul_benchmark.py:46,62 and
+ * matmul_scaling_benchmark.py:79,92,188,211, and torch.bmm(A, B) at
+ * matmul_scaling_benchmark.py:120,142 (batch > 1).
+ *
+ *   A: M x K, leading dimension lda (elements), batch stride strideA
+ *   B: K x N, leading dimension ldb,            batch stride strideB
+ *   C: M x N, leading dimension ldc,            batch stride strideC
+ *   dtype: b2mm_dtype, same for A, B and C.
+ *
+ * Requirements: pointers 16-byte aligned; lda/ldb/ldc and batch strides
+ * multiples of 16 bytes; M, N, K >= 1 (batch == 0 is a no-op, matching
+ * torch.bmm on empty tensors — matmul_scaling_benchmark.py:111 at ws=8).
+ * Rows/columns/K that do not fill a tile are handled in-kernel (TMA
+ * zero-fill / clipped stores); nothing is padded by the caller.
+ *
+ * workspace: only read when b2mm_gemm_workspace_bytes(...) > 0.
+ */
+B2MM_API int b2mm_gemm(const void* A, const void* B, void* C,
+              int64_t M, int64_t N, int64_t K,
+              int64_t lda, int64_t ldb, int64_t ldc,
+              int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC,
+              int dtype, void* workspace, size_t workspace_bytes,
+              b2mm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Collectives.  The communicator wraps an ncclComm_t owned by the library
+ * (libnccl is dlopen'ed on first use; the same libnccl.so.2 torch loaded).
+ * ---------------------------------------------------------------------- */
+
+#define B2MM_UNIQUE_ID_BYTES 128
+
+/* Fill a 128-byte NCCL unique id (host memory).  Rank 0 calls this and ships
+ * the bytes to the other ranks through the existing torch process group —
+ * the rendezvous matmul_scaling_benchmark.py:15-24 already performs. */
+B2MM_API int b2mm_comm_unique_id(void* id_out_128_bytes);
+
+/* Collective over all `world` ranks.  The current CUDA device is the rank's. */
+B2MM_API int b2mm_comm_init(const void* id_128_bytes, int rank, int world, void** comm_out);
+
+/* Replaces dist.destroy_process_group() for this communicator
+ * (matmul_scaling_benchmark.py:59-61). */
+B2MM_API int b2mm_comm_destroy(void* comm);
+
+/* In-place sum over ranks.  Replaces dist.all_reduce(C, op=SUM) at
+ * matmul_scaling_benchmark.py:125,150. */
+B2MM_API int b2mm_all_reduce_sum(void* comm, void* buf, int64_t count, int dtype, b2mm_stream_t stream);
+
+/* recv is ONE contiguous buffer of world slabs, slab r = rank r's `send`
+ * (count_per_rank elements each).  Replaces dist.all_gather(list, C_local) at
+ * matmul_scaling_benchmark.py:194,221 without torch's flatten-and-copy. */
+B2MM_API int b2mm_all_gather(void* comm, const void* send, void* recv_slabs,
+                    int64_t count_per_rank, int dtype, b2mm_stream_t stream);
+
+/*
+ * matrix_parallel with the gather pipelined behind compute
+ * (after backup/matmul_overlap_benchmark.py:93-180, made race-free):
+ * C_local = A * B_local is computed in `n_panels` row panels on `compute`;
+ * as each panel finishes, its rows are all-gathered on `comm_stream` into
+ * recv_slabs ([world][M][n_local], the same layout b2mm_all_gather produces).
+ * On return `compute` has been made to wait for the last gather.
+ */
+B2MM_API int b2mm_gemm_allgather_overlap(void* comm,
+                                const void* A, const void* B_local, void* C_local, void* recv_slabs,
+                                int64_t M, int64_t n_local, int64_t K,
+                                int dtype, int n_panels,
+                                void* workspace, size_t workspace_bytes,
+                                b2mm_stream_t compute, b2mm_stream_t comm_stream);
+
+/*
+ * batch_parallel with the reduction pipelined behind compute: each local
+ * batch element (or row panel, when local batch is 1) is all-reduced on
+ * `comm_stream` as soon as its GEMM has finished on `compute`.
+ */
+B2MM_API int b2mm_gemm_allreduce_overlap(void* comm,
+                                const void* A, const void* B, void* C,
+                                int64_t N, int64_t local_batch,
+                                int dtype, int n_panels,
+                                void* workspace, size_t workspace_bytes,
+                                b2mm_stream_t compute, b2mm_stream_t comm_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2MM_H_ */

@@ -1,0 +1,269 @@
+// C-ABI entry points for the GEMM path (see include/b2mm.h).
+// Host side only: argument checks, TMA tensor-map encoding, kernel selection
+// and launch.  Nothing here synchronises the host with the device.
+#include "../../include/b2mm.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+#include "common.h"
+#include "gemm_sm100.cuh"
+
+namespace b2mm {
+
+thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int dtype_bytes(int dtype) {
+  switch (dtype) {
+    case B2MM_BF16:
+    case B2MM_FP16: return 2;
+    case B2MM_FP32: return 4;
+    default: return 0;
+  }
+}
+
+// ------------------------------------------------------------ driver entry
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 3-D map over a (batch, rows, cols) row-major array: dims {cols, rows, batch}.
+static int make_map(CUtensorMap* map, const void* ptr, int dtype, int64_t cols, int64_t rows, int64_t batch,
+                    int64_t ld, int64_t batch_stride, uint32_t box_cols, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return fail(B2MM_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const int es = dtype_bytes(dtype);
+  CUtensorMapDataType dt = dtype == B2MM_BF16   ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                           : dtype == B2MM_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)(batch > 0 ? batch : 1)};
+  if (batch <= 1) batch_stride = rows * ld;
+  cuuint64_t strides[2] = {(cuuint64_t)ld * es, (cuuint64_t)batch_stride * es};
+  cuuint32_t box[3] = {box_cols, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(map, dt, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(B2MM_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d): cols=%lld rows=%lld batch=%lld ld=%lld", (int)r,
+                (long long)cols, (long long)rows, (long long)batch, (long long)ld);
+  return B2MM_OK;
+}
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+int device_sm_count() {
+  static int cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+struct Operands {
+  const void *A, *B, *A_lo, *B_lo;
+  void* C;
+  int64_t M, N, K, lda, ldb, ldc, batch, sA, sB, sC;
+  int dtype;
+};
+
+template <class Cfg>
+static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
+  CUtensorMap tmA, tmB, tmC, tmA_lo, tmB_lo;
+  int rc;
+  if ((rc = make_map(&tmA, o.A, o.dtype, o.K, o.M, o.batch, o.lda, o.sA, Cfg::BLOCK_K, Cfg::CTA_M))) return rc;
+  if ((rc = make_map(&tmB, o.B, o.dtype, o.N, o.K, o.batch, o.ldb, o.sB, Cfg::N_ATOM, Cfg::BLOCK_K))) return rc;
+  if ((rc = make_map(&tmC, o.C, o.dtype, o.N, o.M, o.batch, o.ldc, o.sC, Cfg::OUT_COLS, 32))) return rc;
+  if (Cfg::kSplit == 2) {
+    if ((rc = make_map(&tmA_lo, o.A_lo, o.dtype, o.K, o.M, o.batch, o.lda, o.sA, Cfg::BLOCK_K, Cfg::CTA_M))) return rc;
+    if ((rc = make_map(&tmB_lo, o.B_lo, o.dtype, o.N, o.K, o.batch, o.ldb, o.sB, Cfg::N_ATOM, Cfg::BLOCK_K))) return rc;
+  } else {
+    tmA_lo = tmA;
+    tmB_lo = tmB;
+  }
+
+  GemmParams p;
+  p.M = (int)o.M; p.N = (int)o.N; p.K = (int)o.K; p.batch = (int)o.batch;
+  p.m_tiles = (int)((o.M + Cfg::TILE_M - 1) / Cfg::TILE_M);
+  p.n_tiles = (int)((o.N + Cfg::BLOCK_N - 1) / Cfg::BLOCK_N);
+  p.num_tiles = p.m_tiles * p.n_tiles * p.batch;
+  p.num_kb = (int)((o.K + Cfg::BLOCK_K - 1) / Cfg::BLOCK_K);
+  p.group_m = env_int("B2MM_GROUP_M", 8);
+  if (p.group_m < 1) p.group_m = 1;
+  const InKind kind = o.dtype == B2MM_BF16 ? InKind::BF16 : o.dtype == B2MM_FP16 ? InKind::FP16 : InKind::TF32;
+  p.idesc = make_idesc(kind, Cfg::TILE_M, Cfg::BLOCK_N);
+
+  int sms = device_sm_count();
+  if (sms <= 0) return fail(B2MM_ERR_CUDA, "cannot query SM count");
+  if (max_sms > 0 && max_sms < sms) sms = max_sms;
+  int clusters = sms / Cfg::kCtaGroup;
+  if (clusters > p.num_tiles) clusters = p.num_tiles;
+  if (clusters < 1) clusters = 1;
+
+  auto kern = gemm_kernel<Cfg>;
+  static thread_local int attr_dev_mask_lo = 0;  // devices 0..31 that already have the smem attribute
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 32 || !(attr_dev_mask_lo & (1 << dev))) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "cudaFuncSetAttribute(smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+    if (dev < 32) attr_dev_mask_lo |= (1 << dev);
+  }
+
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)(clusters * Cfg::kCtaGroup), 1, 1);
+  cfg.blockDim = dim3(Cfg::kThreads, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = Cfg::kCtaGroup;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmA_lo, tmB_lo, p);
+  if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
+  count_launch(1);
+  return B2MM_OK;
+}
+
+// Units of "tile columns x waves": a cheap model for picking BLOCK_N.
+static int64_t wave_cost(const Operands& o, int tile_m, int block_n, int clusters) {
+  const int64_t tiles = ((o.M + tile_m - 1) / tile_m) * ((o.N + block_n - 1) / block_n) * o.batch;
+  const int64_t waves = (tiles + clusters - 1) / clusters;
+  return waves * block_n;
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+size_t gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype) {
+  if (dtype != B2MM_FP32 || batch <= 0) return 0;
+  const size_t a = align_up((size_t)batch * M * K * 4, 256);
+  const size_t b = align_up((size_t)batch * K * N * 4, 256);
+  return 2 * a + 2 * b;
+}
+
+int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+              int64_t ldc, int64_t batch, int64_t sA, int64_t sB, int64_t sC, int dtype, void* workspace,
+              size_t workspace_bytes, int max_sms, cudaStream_t stream) {
+  const int es = dtype_bytes(dtype);
+  if (es == 0) return fail(B2MM_ERR_BAD_ARG, "unknown dtype %d", dtype);
+  if (batch < 0 || M < 0 || N < 0 || K < 0) return fail(B2MM_ERR_BAD_ARG, "negative size");
+  if (batch == 0 || M == 0 || N == 0) return B2MM_OK;  // empty output: nothing to do (torch.bmm on b=0)
+  if (K == 0) return fail(B2MM_ERR_UNSUPPORTED, "K == 0 (zero-fill of C) is not implemented");
+  if (!A || !B || !C) return fail(B2MM_ERR_BAD_ARG, "null operand pointer");
+  if (lda < K || ldb < N || ldc < N) return fail(B2MM_ERR_BAD_ARG, "leading dimension smaller than row length");
+  if (((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) return fail(B2MM_ERR_UNSUPPORTED, "operands must be 16-byte aligned");
+  if ((lda * es) % 16 || (ldb * es) % 16 || (ldc * es) % 16)
+    return fail(B2MM_ERR_UNSUPPORTED, "leading dimensions must be multiples of 16 bytes (lda=%lld ldb=%lld ldc=%lld, %d-byte elements)",
+                (long long)lda, (long long)ldb, (long long)ldc, es);
+  if (batch > 1 && ((sA * es) % 16 || (sB * es) % 16 || (sC * es) % 16))
+    return fail(B2MM_ERR_UNSUPPORTED, "batch strides must be multiples of 16 bytes");
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX || batch > 65535)
+    return fail(B2MM_ERR_UNSUPPORTED, "dimension too large");
+
+  Operands o{A, B, nullptr, nullptr, C, M, N, K, lda, ldb, ldc, batch, sA, sB, sC, dtype};
+  const int sms = device_sm_count();
+  int clusters = (max_sms > 0 && max_sms < sms ? max_sms : sms) / 2;
+  if (clusters < 1) clusters = 1;
+
+  if (dtype == B2MM_FP32) {
+    const size_t need = gemm_workspace_bytes(M, N, K, batch, dtype);
+    if (!workspace || workspace_bytes < need)
+      return fail(B2MM_ERR_WORKSPACE, "fp32 GEMM needs %zu bytes of workspace, got %zu", need, workspace_bytes);
+    if ((uintptr_t)workspace & 255) return fail(B2MM_ERR_BAD_ARG, "workspace must be 256-byte aligned");
+    const size_t a_bytes = align_up((size_t)batch * M * K * 4, 256);
+    const size_t b_bytes = align_up((size_t)batch * K * N * 4, 256);
+    char* w = (char*)workspace;
+    float* a_hi = (float*)w;
+    float* a_lo = (float*)(w + a_bytes);
+    float* b_hi = (float*)(w + 2 * a_bytes);
+    float* b_lo = (float*)(w + 2 * a_bytes + b_bytes);
+    const int blocks = (sms > 0 ? sms : 148) * 8;
+    split_tf32_kernel<<<blocks, 256, 0, stream>>>((const float*)A, a_hi, a_lo, M, K, lda, batch, sA);
+    split_tf32_kernel<<<blocks, 256, 0, stream>>>((const float*)B, b_hi, b_lo, K, N, ldb, batch, sB);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "split launch failed: %s", cudaGetErrorString(e));
+    count_launch(2);
+    o.A = a_hi; o.A_lo = a_lo; o.lda = K; o.sA = M * K;
+    o.B = b_hi; o.B_lo = b_lo; o.ldb = N; o.sB = K * N;
+    return launch_cfg<GemmConfig<2, 256, 4, 2, float>>(o, max_sms, stream);
+  }
+
+  int block_n = env_int("B2MM_BLOCK_N", 0);
+  if (block_n != 128 && block_n != 256)
+    block_n = wave_cost(o, 256, 128, clusters) < wave_cost(o, 256, 256, clusters) ? 128 : 256;
+  const int cta_group = env_int("B2MM_CTA_GROUP", 2);
+
+  if (dtype == B2MM_BF16) {
+    if (cta_group == 1) return launch_cfg<GemmConfig<1, 256, 2, 1, __nv_bfloat16>>(o, max_sms, stream);
+    if (block_n == 128) return launch_cfg<GemmConfig<2, 128, 2, 1, __nv_bfloat16>>(o, max_sms, stream);
+    return launch_cfg<GemmConfig<2, 256, 2, 1, __nv_bfloat16>>(o, max_sms, stream);
+  } else {
+    if (cta_group == 1) return launch_cfg<GemmConfig<1, 256, 2, 1, __half>>(o, max_sms, stream);
+    if (block_n == 128) return launch_cfg<GemmConfig<2, 128, 2, 1, __half>>(o, max_sms, stream);
+    return launch_cfg<GemmConfig<2, 256, 2, 1, __half>>(o, max_sms, stream);
+  }
+}
+
+}  // namespace b2mm
+
+extern "C" {
+
+int b2mm_version(void) { return B2MM_VERSION; }
+
+const char* b2mm_last_error(void) { return b2mm::g_err; }
+
+uint64_t b2mm_launch_count(void) { return b2mm::g_launches.load(std::memory_order_relaxed); }
+
+size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype) {
+  return b2mm::gemm_workspace_bytes(M, N, K, batch, dtype);
+}
+
+int b2mm_gemm(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+              int64_t ldc, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC, int dtype,
+              void* workspace, size_t workspace_bytes, b2mm_stream_t stream) {
+  return b2mm::gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, batch, strideA, strideB, strideC, dtype, workspace,
+                         workspace_bytes, /*max_sms=*/0, (cudaStream_t)stream);
+}
+
+}  // extern "C"

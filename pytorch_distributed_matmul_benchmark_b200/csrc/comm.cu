@@ -1,0 +1,234 @@
+// Collective entry points (see include/b2mm.h) and the stream-pipelined
+// GEMM + collective drivers.  NCCL is loaded with dlopen so that libb2mm.so
+// has no link-time dependency on it: in a torch process the already-loaded
+// libnccl.so.2 (torch's) is the one that answers.
+#include "../../include/b2mm.h"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+#include "common.h"
+
+namespace b2mm {
+
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  bool ok = false;
+};
+
+static NcclApi& nccl() {
+  static NcclApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+      api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (api.handle) break;
+    }
+    if (!api.handle) return;
+#define B2MM_SYM(field, sym)                                              \
+  api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, sym)); \
+  if (!api.field) return;
+    B2MM_SYM(GetUniqueId, "ncclGetUniqueId")
+    B2MM_SYM(CommInitRank, "ncclCommInitRank")
+    B2MM_SYM(CommDestroy, "ncclCommDestroy")
+    B2MM_SYM(AllReduce, "ncclAllReduce")
+    B2MM_SYM(AllGather, "ncclAllGather")
+    B2MM_SYM(Broadcast, "ncclBroadcast")
+    B2MM_SYM(GroupStart, "ncclGroupStart")
+    B2MM_SYM(GroupEnd, "ncclGroupEnd")
+    B2MM_SYM(GetErrorString, "ncclGetErrorString")
+#undef B2MM_SYM
+    api.ok = true;
+  });
+  return api;
+}
+
+static constexpr int kMaxPanels = 64;
+
+struct Comm {
+  ncclComm_t nccl = nullptr;
+  int rank = 0, world = 1;
+  cudaEvent_t panel_done[kMaxPanels];
+  cudaEvent_t comm_done = nullptr;
+};
+
+static int nccl_fail(const char* what, ncclResult_t r) {
+  return fail(B2MM_ERR_NCCL, "%s: %s", what, nccl().GetErrorString ? nccl().GetErrorString(r) : "nccl error");
+}
+
+static bool nccl_type(int dtype, ncclDataType_t* t) {
+  switch (dtype) {
+    case B2MM_BF16: *t = ncclBfloat16; return true;
+    case B2MM_FP16: *t = ncclFloat16; return true;
+    case B2MM_FP32: *t = ncclFloat32; return true;
+    default: return false;
+  }
+}
+
+static int comm_sms() {
+  const char* v = getenv("B2MM_COMM_SMS");
+  int n = (v && *v) ? atoi(v) : 16;
+  return n < 0 ? 0 : n;
+}
+
+}  // namespace b2mm
+
+using namespace b2mm;
+
+extern "C" {
+
+int b2mm_comm_unique_id(void* id_out) {
+  if (!id_out) return fail(B2MM_ERR_BAD_ARG, "null id buffer");
+  static_assert(sizeof(ncclUniqueId) == B2MM_UNIQUE_ID_BYTES, "ncclUniqueId size");
+  if (!nccl().ok) return fail(B2MM_ERR_NCCL, "libnccl.so.2 could not be loaded: %s", dlerror());
+  ncclUniqueId id;
+  ncclResult_t r = nccl().GetUniqueId(&id);
+  if (r != ncclSuccess) return nccl_fail("ncclGetUniqueId", r);
+  memcpy(id_out, &id, sizeof(id));
+  return B2MM_OK;
+}
+
+int b2mm_comm_init(const void* id_bytes, int rank, int world, void** comm_out) {
+  if (!id_bytes || !comm_out || world < 1 || rank < 0 || rank >= world) return fail(B2MM_ERR_BAD_ARG, "bad comm_init argument");
+  if (!nccl().ok) return fail(B2MM_ERR_NCCL, "libnccl.so.2 could not be loaded");
+  ncclUniqueId id;
+  memcpy(&id, id_bytes, sizeof(id));
+  Comm* c = new Comm();
+  c->rank = rank;
+  c->world = world;
+  ncclResult_t r = nccl().CommInitRank(&c->nccl, world, id, rank);
+  if (r != ncclSuccess) {
+    delete c;
+    return nccl_fail("ncclCommInitRank", r);
+  }
+  for (int i = 0; i < kMaxPanels; ++i)
+    if (cudaEventCreateWithFlags(&c->panel_done[i], cudaEventDisableTiming) != cudaSuccess) {
+      delete c;
+      return fail(B2MM_ERR_CUDA, "cudaEventCreate failed");
+    }
+  cudaEventCreateWithFlags(&c->comm_done, cudaEventDisableTiming);
+  *comm_out = c;
+  return B2MM_OK;
+}
+
+int b2mm_comm_destroy(void* comm) {
+  if (!comm) return B2MM_OK;
+  Comm* c = (Comm*)comm;
+  for (int i = 0; i < kMaxPanels; ++i) cudaEventDestroy(c->panel_done[i]);
+  if (c->comm_done) cudaEventDestroy(c->comm_done);
+  if (c->nccl) nccl().CommDestroy(c->nccl);
+  delete c;
+  return B2MM_OK;
+}
+
+int b2mm_all_reduce_sum(void* comm, void* buf, int64_t count, int dtype, b2mm_stream_t stream) {
+  Comm* c = (Comm*)comm;
+  ncclDataType_t t;
+  if (!c || count < 0 || !nccl_type(dtype, &t)) return fail(B2MM_ERR_BAD_ARG, "bad all_reduce argument");
+  if (count == 0) return B2MM_OK;  // batch_parallel at ws=8: local batch 0 (matmul_scaling_benchmark.py:111)
+  if (!buf) return fail(B2MM_ERR_BAD_ARG, "null buffer");
+  ncclResult_t r = nccl().AllReduce(buf, buf, (size_t)count, t, ncclSum, c->nccl, (cudaStream_t)stream);
+  if (r != ncclSuccess) return nccl_fail("ncclAllReduce", r);
+  return B2MM_OK;
+}
+
+int b2mm_all_gather(void* comm, const void* send, void* recv_slabs, int64_t count_per_rank, int dtype,
+                    b2mm_stream_t stream) {
+  Comm* c = (Comm*)comm;
+  ncclDataType_t t;
+  if (!c || count_per_rank < 0 || !nccl_type(dtype, &t)) return fail(B2MM_ERR_BAD_ARG, "bad all_gather argument");
+  if (count_per_rank == 0) return B2MM_OK;
+  if (!send || !recv_slabs) return fail(B2MM_ERR_BAD_ARG, "null buffer");
+  ncclResult_t r = nccl().AllGather(send, recv_slabs, (size_t)count_per_rank, t, c->nccl, (cudaStream_t)stream);
+  if (r != ncclSuccess) return nccl_fail("ncclAllGather", r);
+  return B2MM_OK;
+}
+
+int b2mm_gemm_allgather_overlap(void* comm, const void* A, const void* B_local, void* C_local, void* recv_slabs,
+                                int64_t M, int64_t n_local, int64_t K, int dtype, int n_panels, void* workspace,
+                                size_t workspace_bytes, b2mm_stream_t compute_, b2mm_stream_t comm_stream_) {
+  Comm* c = (Comm*)comm;
+  ncclDataType_t t;
+  if (!c || !nccl_type(dtype, &t)) return fail(B2MM_ERR_BAD_ARG, "bad comm or dtype");
+  if (n_panels < 1 || n_panels > kMaxPanels) return fail(B2MM_ERR_BAD_ARG, "n_panels must be in [1, %d]", kMaxPanels);
+  if (M % n_panels) return fail(B2MM_ERR_UNSUPPORTED, "M=%lld is not divisible by n_panels=%d", (long long)M, n_panels);
+  cudaStream_t compute = (cudaStream_t)compute_, cs = (cudaStream_t)comm_stream_;
+  const int es = dtype_bytes(dtype);
+  const int64_t mp = M / n_panels;
+  const int64_t slab = M * n_local;  // elements per rank in recv_slabs
+  const int sms = device_sm_count();
+  const int gemm_sms = sms - comm_sms() > 2 ? sms - comm_sms() : sms;
+  for (int i = 0; i < n_panels; ++i) {
+    const char* a = (const char*)A + (size_t)i * mp * K * es;
+    char* cl = (char*)C_local + (size_t)i * mp * n_local * es;
+    int rc = gemm_impl(a, B_local, cl, mp, n_local, K, K, n_local, n_local, 1, 0, 0, 0, dtype, workspace,
+                       workspace_bytes, gemm_sms, compute);
+    if (rc) return rc;
+    if (cudaEventRecord(c->panel_done[i], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
+    if (cudaStreamWaitEvent(cs, c->panel_done[i], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
+    // all_gather of row panel i: slab r receives rank r's panel at the same row offset.
+    ncclResult_t r = nccl().GroupStart();
+    if (r != ncclSuccess) return nccl_fail("ncclGroupStart", r);
+    for (int root = 0; root < c->world; ++root) {
+      char* dst = (char*)recv_slabs + ((size_t)root * slab + (size_t)i * mp * n_local) * es;
+      r = nccl().Broadcast(cl, dst, (size_t)(mp * n_local), t, root, c->nccl, cs);
+      if (r != ncclSuccess) { nccl().GroupEnd(); return nccl_fail("ncclBroadcast", r); }
+    }
+    r = nccl().GroupEnd();
+    if (r != ncclSuccess) return nccl_fail("ncclGroupEnd", r);
+  }
+  if (cudaEventRecord(c->comm_done, cs) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
+  if (cudaStreamWaitEvent(compute, c->comm_done, 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
+  return B2MM_OK;
+}
+
+int b2mm_gemm_allreduce_overlap(void* comm, const void* A, const void* B, void* C, int64_t N, int64_t local_batch,
+                                int dtype, int n_panels, void* workspace, size_t workspace_bytes,
+                                b2mm_stream_t compute_, b2mm_stream_t comm_stream_) {
+  Comm* c = (Comm*)comm;
+  ncclDataType_t t;
+  if (!c || !nccl_type(dtype, &t)) return fail(B2MM_ERR_BAD_ARG, "bad comm or dtype");
+  if (local_batch == 0) return B2MM_OK;
+  if (n_panels < 1 || n_panels * local_batch > kMaxPanels)
+    return fail(B2MM_ERR_BAD_ARG, "n_panels * local_batch must be in [1, %d]", kMaxPanels);
+  if (N % n_panels) return fail(B2MM_ERR_UNSUPPORTED, "N=%lld is not divisible by n_panels=%d", (long long)N, n_panels);
+  cudaStream_t compute = (cudaStream_t)compute_, cs = (cudaStream_t)comm_stream_;
+  const int es = dtype_bytes(dtype);
+  const int64_t mp = N / n_panels;
+  const int sms = device_sm_count();
+  const int gemm_sms = sms - comm_sms() > 2 ? sms - comm_sms() : sms;
+  int ev = 0;
+  for (int64_t b = 0; b < local_batch; ++b) {
+    for (int i = 0; i < n_panels; ++i, ++ev) {
+      const char* a = (const char*)A + ((size_t)b * N * N + (size_t)i * mp * N) * es;
+      const char* bb = (const char*)B + (size_t)b * N * N * es;
+      char* cc = (char*)C + ((size_t)b * N * N + (size_t)i * mp * N) * es;
+      int rc = gemm_impl(a, bb, cc, mp, N, N, N, N, N, 1, 0, 0, 0, dtype, workspace, workspace_bytes, gemm_sms, compute);
+      if (rc) return rc;
+      if (cudaEventRecord(c->panel_done[ev], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
+      if (cudaStreamWaitEvent(cs, c->panel_done[ev], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
+      ncclResult_t r = nccl().AllReduce(cc, cc, (size_t)(mp * N), t, ncclSum, c->nccl, cs);
+      if (r != ncclSuccess) return nccl_fail("ncclAllReduce", r);
+    }
+  }
+  if (cudaEventRecord(c->comm_done, cs) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
+  if (cudaStreamWaitEvent(compute, c->comm_done, 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
+  return B2MM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,210 @@
+"""Host-side operators with the signatures the reference scripts use.
+
+`matmul` / `bmm` stand where the reference calls `torch.matmul` / `torch.bmm`
+(matmul_benchmark.py:62, matmul_scaling_benchmark.py:92,142,211); `Communicator`
+stands where it calls `dist.all_reduce` / `dist.all_gather`
+(matmul_scaling_benchmark.py:150,221).  torch is used for device memory and
+streams only: every operator hands raw device pointers to libb2mm.so.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+
+_DTYPES = {torch.bfloat16: _lib.BF16, torch.float16: _lib.FP16, torch.float32: _lib.FP32}
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"b2mm supports bfloat16/float16/float32, got {t.dtype}") from None
+
+
+def _stream_ptr(stream: Optional[torch.cuda.Stream] = None) -> int:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def _require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError("b2mm operators take CUDA tensors only (there is no CPU fallback)")
+
+
+_workspaces = {}
+
+
+def workspace_for(M: int, N: int, K: int, batch: int, dtype_code: int, device: torch.device):
+    """Scratch for the fp32 (3xTF32) path; one cached buffer per device, grown on demand."""
+    need = int(_lib.load().b2mm_gemm_workspace_bytes(M, N, K, batch, dtype_code))
+    if need == 0:
+        return None, 0
+    key = (device.type, device.index)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < need:
+        _workspaces[key] = buf = torch.empty(need, dtype=torch.uint8, device=device)
+    return buf, need
+
+
+def release_workspaces() -> None:
+    """Drop cached scratch (the reference calls torch.cuda.empty_cache() after each size)."""
+    _workspaces.clear()
+
+
+def _rows_ok(t: torch.Tensor) -> bool:
+    return t.stride(-1) == 1 and t.stride(-2) >= t.shape[-1]
+
+
+def matmul(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """C = A @ B for 2-D row-major tensors; allocates C like torch.matmul unless `out` is given."""
+    if A.dim() == 3 and B.dim() == 3:
+        return bmm(A, B, out=out)
+    if A.dim() != 2 or B.dim() != 2:
+        raise RuntimeError(f"matmul expects 2-D (or 3-D batched) operands, got {A.dim()}-D and {B.dim()}-D")
+    _require_cuda(A, B)
+    if A.dtype != B.dtype:
+        raise RuntimeError(f"expected both operands to have the same dtype, got {A.dtype} and {B.dtype}")
+    M, K = A.shape
+    K2, N = B.shape
+    if K != K2:
+        raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({M}x{K} and {K2}x{N})")
+    if not _rows_ok(A):
+        A = A.contiguous()
+    if not _rows_ok(B):
+        B = B.contiguous()
+    if out is None:
+        out = torch.empty((M, N), dtype=A.dtype, device=A.device)
+    elif out.shape != (M, N) or out.dtype != A.dtype or not _rows_ok(out):
+        raise RuntimeError("out has the wrong shape, dtype or layout")
+    code = _dtype_code(A)
+    if M == 0 or N == 0:
+        return out
+    if K == 0:
+        return out.zero_()
+    ws, ws_bytes = workspace_for(M, N, K, 1, code, A.device)
+    with torch.cuda.device(A.device):
+        _lib.check(_lib.load().b2mm_gemm(
+            A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, A.stride(0), B.stride(0), out.stride(0),
+            1, 0, 0, 0, code, ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr()))
+    return out
+
+
+def bmm(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """C[b] = A[b] @ B[b]; mirrors torch.bmm, including empty batches."""
+    if A.dim() != 3 or B.dim() != 3:
+        raise RuntimeError("batch1 and batch2 must be 3D tensors")
+    _require_cuda(A, B)
+    if A.dtype != B.dtype:
+        raise RuntimeError(f"expected both operands to have the same dtype, got {A.dtype} and {B.dtype}")
+    b, M, K = A.shape
+    b2, K2, N = B.shape
+    if b != b2 or K != K2:
+        raise RuntimeError(f"batch1 and batch2 shapes cannot be multiplied ({tuple(A.shape)} and {tuple(B.shape)})")
+    if not _rows_ok(A):
+        A = A.contiguous()
+    if not _rows_ok(B):
+        B = B.contiguous()
+    if out is None:
+        out = torch.empty((b, M, N), dtype=A.dtype, device=A.device)
+    elif out.shape != (b, M, N) or out.dtype != A.dtype or not _rows_ok(out):
+        raise RuntimeError("out has the wrong shape, dtype or layout")
+    code = _dtype_code(A)
+    if b == 0 or M == 0 or N == 0:
+        return out
+    if K == 0:
+        return out.zero_()
+    ws, ws_bytes = workspace_for(M, N, K, b, code, A.device)
+    with torch.cuda.device(A.device):
+        _lib.check(_lib.load().b2mm_gemm(
+            A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, A.stride(1), B.stride(1), out.stride(1),
+            b, A.stride(0), B.stride(0), out.stride(0), code,
+            ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr()))
+    return out
+
+
+class Communicator:
+    """An ncclComm_t owned by libb2mm.so, bootstrapped over an existing torch process group.
+
+    torch.distributed performs the rendezvous exactly as the reference does
+    (matmul_scaling_benchmark.py:15-24); it is then only used to ship the NCCL
+    unique id.  Payload collectives go through the C ABI.
+    """
+
+    def __init__(self, rank: int, world_size: int, device: torch.device):
+        import torch.distributed as dist
+        self.rank, self.world_size, self.device = rank, world_size, device
+        self._comm = ctypes.c_void_p()
+        lib = _lib.load()
+        id_buf = (ctypes.c_ubyte * _lib.UNIQUE_ID_BYTES)()
+        if rank == 0:
+            _lib.check(lib.b2mm_comm_unique_id(ctypes.cast(id_buf, ctypes.c_void_p)))
+        payload = [bytes(id_buf)]
+        dist.broadcast_object_list(payload, src=0)
+        id_buf = (ctypes.c_ubyte * _lib.UNIQUE_ID_BYTES).from_buffer_copy(payload[0])
+        with torch.cuda.device(device):
+            _lib.check(lib.b2mm_comm_init(ctypes.cast(id_buf, ctypes.c_void_p), rank, world_size,
+                                          ctypes.byref(self._comm)))
+        self.comm_stream = torch.cuda.Stream(device=device, priority=-1)
+
+    def destroy(self) -> None:
+        if self._comm:
+            _lib.check(_lib.load().b2mm_comm_destroy(self._comm))
+            self._comm = ctypes.c_void_p()
+
+    def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place SUM, like dist.all_reduce(t, op=ReduceOp.SUM)."""
+        _require_cuda(t)
+        if not t.is_contiguous():
+            raise RuntimeError("all_reduce needs a contiguous tensor")
+        _lib.check(_lib.load().b2mm_all_reduce_sum(self._comm, t.data_ptr() if t.numel() else None, t.numel(),
+                                                   _dtype_code(t), _stream_ptr()))
+        return t
+
+    def all_gather_into(self, slabs: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
+        """slabs[r] = rank r's t; `slabs` is one contiguous (world, *t.shape) tensor."""
+        _require_cuda(slabs, t)
+        if not (slabs.is_contiguous() and t.is_contiguous()):
+            raise RuntimeError("all_gather needs contiguous tensors")
+        if slabs.numel() != t.numel() * self.world_size or slabs.dtype != t.dtype:
+            raise RuntimeError("slabs must hold world_size copies of the input")
+        _lib.check(_lib.load().b2mm_all_gather(self._comm, t.data_ptr(), slabs.data_ptr(), t.numel(), _dtype_code(t),
+                                               _stream_ptr()))
+        return slabs
+
+    def all_gather(self, t: torch.Tensor) -> List[torch.Tensor]:
+        """Returns the list dist.all_gather(list, t) would fill (views of one slab buffer)."""
+        slabs = torch.empty((self.world_size,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+        self.all_gather_into(slabs, t)
+        return list(slabs.unbind(0))
+
+    def matmul_allgather_overlap(self, A: torch.Tensor, B_local: torch.Tensor, C_local: torch.Tensor,
+                                 slabs: torch.Tensor, n_panels: int = 4) -> torch.Tensor:
+        """C_local = A @ B_local in row panels, each panel gathered on the comm stream while the next computes."""
+        _require_cuda(A, B_local, C_local, slabs)
+        M, K = A.shape
+        n_local = B_local.shape[1]
+        code = _dtype_code(A)
+        ws, ws_bytes = workspace_for(M // n_panels, n_local, K, 1, code, A.device)
+        self.comm_stream.wait_stream(torch.cuda.current_stream())
+        _lib.check(_lib.load().b2mm_gemm_allgather_overlap(
+            self._comm, A.data_ptr(), B_local.data_ptr(), C_local.data_ptr(), slabs.data_ptr(), M, n_local, K, code,
+            n_panels, ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(),
+            self.comm_stream.cuda_stream))
+        return slabs
+
+    def bmm_allreduce_overlap(self, A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, n_panels: int = 4) -> torch.Tensor:
+        """C = bmm(A, B) with each panel all-reduced on the comm stream while the next computes."""
+        _require_cuda(A, B, C)
+        b, N, _ = A.shape
+        code = _dtype_code(A)
+        ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)
+        self.comm_stream.wait_stream(torch.cuda.current_stream())
+        _lib.check(_lib.load().b2mm_gemm_allreduce_overlap(
+            self._comm, A.data_ptr(), B.data_ptr(), C.data_ptr(), N, b, code, n_panels,
+            ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(), self.comm_stream.cuda_stream))
+        return C

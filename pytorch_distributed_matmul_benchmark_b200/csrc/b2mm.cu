@@ -29,6 +29,8 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
+unsigned long long* g_trace = nullptr;  // set by b2mm_debug_set_trace (tools only)
+
 void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 int dtype_bytes(int dtype) {
@@ -109,11 +111,19 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   CUtensorMap tmA, tmB, tmC, tmA_lo, tmB_lo;
   int rc;
   if ((rc = make_map(&tmA, o.A, o.dtype, o.K, o.M, o.batch, o.lda, o.sA, Cfg::BLOCK_K, Cfg::CTA_M))) return rc;
-  if ((rc = make_map(&tmB, o.B, o.dtype, o.N, o.K, o.batch, o.ldb, o.sB, Cfg::N_ATOM, Cfg::BLOCK_K))) return rc;
+  if (Cfg::kBKMajor) {  // B^T: N rows of K
+    if ((rc = make_map(&tmB, o.B, o.dtype, o.K, o.N, o.batch, o.ldb, o.sB, Cfg::BLOCK_K, Cfg::LOAD_N))) return rc;
+  } else {
+    if ((rc = make_map(&tmB, o.B, o.dtype, o.N, o.K, o.batch, o.ldb, o.sB, Cfg::N_ATOM, Cfg::BLOCK_K))) return rc;
+  }
   if ((rc = make_map(&tmC, o.C, o.dtype, o.N, o.M, o.batch, o.ldc, o.sC, Cfg::OUT_COLS, 32))) return rc;
   if (Cfg::kSplit == 2) {
     if ((rc = make_map(&tmA_lo, o.A_lo, o.dtype, o.K, o.M, o.batch, o.lda, o.sA, Cfg::BLOCK_K, Cfg::CTA_M))) return rc;
-    if ((rc = make_map(&tmB_lo, o.B_lo, o.dtype, o.N, o.K, o.batch, o.ldb, o.sB, Cfg::N_ATOM, Cfg::BLOCK_K))) return rc;
+    if (Cfg::kBKMajor) {
+      if ((rc = make_map(&tmB_lo, o.B_lo, o.dtype, o.K, o.N, o.batch, o.ldb, o.sB, Cfg::BLOCK_K, Cfg::LOAD_N))) return rc;
+    } else {
+      if ((rc = make_map(&tmB_lo, o.B_lo, o.dtype, o.N, o.K, o.batch, o.ldb, o.sB, Cfg::N_ATOM, Cfg::BLOCK_K))) return rc;
+    }
   } else {
     tmA_lo = tmA;
     tmB_lo = tmB;
@@ -128,13 +138,20 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   p.group_m = env_int("B2MM_GROUP_M", 8);
   if (p.group_m < 1) p.group_m = 1;
   const InKind kind = o.dtype == B2MM_BF16 ? InKind::BF16 : o.dtype == B2MM_FP16 ? InKind::FP16 : InKind::TF32;
-  p.idesc = make_idesc(kind, Cfg::TILE_M, Cfg::BLOCK_N);
+  p.idesc = make_idesc(kind, 128 * Cfg::kCtaGroup, Cfg::BLOCK_N, Cfg::kBKMajor);
+  static const uint64_t kHints[3] = {ptx::kEvictNormal, ptx::kEvictFirst, ptx::kEvictLast};
+  p.hint_a = kHints[env_int("B2MM_HINT_A", 0) % 3];
+  p.hint_b = kHints[env_int("B2MM_HINT_B", 0) % 3];
+  p.trace = g_trace;
+  // Dynamic (hardware work-stealing) scheduling unless the caller capped the SMs.
+  const char* sched = getenv("B2MM_SCHED");
+  p.dynamic = (max_sms > 0 || (sched && !strcmp(sched, "static"))) ? 0 : 1;
 
   int sms = device_sm_count();
   if (sms <= 0) return fail(B2MM_ERR_CUDA, "cannot query SM count");
   if (max_sms > 0 && max_sms < sms) sms = max_sms;
   int clusters = sms / Cfg::kCtaGroup;
-  if (clusters > p.num_tiles) clusters = p.num_tiles;
+  if (clusters > p.num_tiles || p.dynamic) clusters = p.num_tiles;
   if (clusters < 1) clusters = 1;
 
   auto kern = gemm_kernel<Cfg>;
@@ -220,26 +237,39 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
     float* b_lo = (float*)(w + 2 * a_bytes + b_bytes);
     const int blocks = (sms > 0 ? sms : 148) * 8;
     split_tf32_kernel<<<blocks, 256, 0, stream>>>((const float*)A, a_hi, a_lo, M, K, lda, batch, sA);
-    split_tf32_kernel<<<blocks, 256, 0, stream>>>((const float*)B, b_hi, b_lo, K, N, ldb, batch, sB);
+    split_tf32_transpose_kernel<<<blocks, 256, 0, stream>>>((const float*)B, b_hi, b_lo, K, N, ldb, batch, sB);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "split launch failed: %s", cudaGetErrorString(e));
     count_launch(2);
     o.A = a_hi; o.A_lo = a_lo; o.lda = K; o.sA = M * K;
-    o.B = b_hi; o.B_lo = b_lo; o.ldb = N; o.sB = K * N;
-    return launch_cfg<GemmConfig<2, 256, 4, 2, float>>(o, max_sms, stream);
+    o.B = b_hi; o.B_lo = b_lo; o.ldb = K; o.sB = K * N;  // B^T: N x K, packed
+    return launch_cfg<GemmConfig<2, 256, 4, 2, float, /*kBKMajor=*/true>>(o, max_sms, stream);
   }
 
   int block_n = env_int("B2MM_BLOCK_N", 0);
-  if (block_n != 128 && block_n != 256)
-    block_n = wave_cost(o, 256, 128, clusters) < wave_cost(o, 256, 256, clusters) ? 128 : 256;
+  if (block_n != 128 && block_n != 256) {
+    // 256-wide tiles move a third less data from L2 per flop (and the part is power
+    // limited), so the narrow tile has to win clearly on wave quantisation to be picked.
+    const int64_t c128 = wave_cost(o, 256, 128, clusters), c256 = wave_cost(o, 256, 256, clusters);
+    block_n = (c128 * 100 < c256 * 85) ? 128 : 256;
+  }
   const int cta_group = env_int("B2MM_CTA_GROUP", 2);
+
+  // Tall tiles (512 x 256 per CTA pair) whenever the problem still fills the machine with them.
+  int m_blocks = env_int("B2MM_M_BLOCKS", 0);
+  if (m_blocks != 1 && m_blocks != 2) {
+    const int64_t tall_tiles = ((M + 511) / 512) * ((N + 255) / 256) * batch;
+    m_blocks = (tall_tiles >= clusters) ? 2 : 1;
+  }
 
   if (dtype == B2MM_BF16) {
     if (cta_group == 1) return launch_cfg<GemmConfig<1, 256, 2, 1, __nv_bfloat16>>(o, max_sms, stream);
+    if (m_blocks == 2) return launch_cfg<GemmConfig<2, 256, 2, 1, __nv_bfloat16, false, 2>>(o, max_sms, stream);
     if (block_n == 128) return launch_cfg<GemmConfig<2, 128, 2, 1, __nv_bfloat16>>(o, max_sms, stream);
     return launch_cfg<GemmConfig<2, 256, 2, 1, __nv_bfloat16>>(o, max_sms, stream);
   } else {
     if (cta_group == 1) return launch_cfg<GemmConfig<1, 256, 2, 1, __half>>(o, max_sms, stream);
+    if (m_blocks == 2) return launch_cfg<GemmConfig<2, 256, 2, 1, __half, false, 2>>(o, max_sms, stream);
     if (block_n == 128) return launch_cfg<GemmConfig<2, 128, 2, 1, __half>>(o, max_sms, stream);
     return launch_cfg<GemmConfig<2, 256, 2, 1, __half>>(o, max_sms, stream);
   }
@@ -258,6 +288,8 @@ uint64_t b2mm_launch_count(void) { return b2mm::g_launches.load(std::memory_orde
 size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype) {
   return b2mm::gemm_workspace_bytes(M, N, K, batch, dtype);
 }
+
+void b2mm_debug_set_trace(void* device_buffer) { b2mm::g_trace = (unsigned long long*)device_buffer; }
 
 int b2mm_gemm(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
               int64_t ldc, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC, int dtype,

@@ -15,10 +15,26 @@
 //   (256 x BLOCK_N) tile: each CTA loads its own 128 rows of A and HALF of the
 //   B columns; tcgen05.mma.cta_group::2 reads both halves.
 //
-// Warp roles (192 threads)
+// Tile shapes.  kMBlocks == 2 (the default for 16-bit inputs) gives each CTA a
+// 256-row slab: per k-block it loads 32 KB of A and 16 KB of B for 2 x 4 MMAs,
+// 48 B/cycle/SM from L2 instead of the 64 B/cycle/SM of the 128-row slab.  That
+// matters twice on B200: the part is power limited, and at 64 B/cycle/SM some
+// TPCs are L2-bandwidth starved (measured: two SM populations 4 % apart), which
+// lets clusters drift apart in k and destroys their sharing of panels in L2.
+//
+// Warp roles (224 threads)
 //   warp 0      TMA producer (one elected lane)
 //   warp 1      TMEM allocator + MMA issuer (one elected lane, leader CTA only)
 //   warps 2..5  epilogue: tcgen05.ld -> convert -> swizzled smem -> TMA store
+//   warp 6      tile scheduler (one elected lane, leader CTA only; dynamic mode)
+//
+// Tile scheduling.  Static: grid = min(#SM, tiles) CTAs, cluster c takes tiles c, c + C, ...
+// (used when the caller caps the SMs, i.e. when a collective runs beside the GEMM).
+// Dynamic (default): the grid has one cluster per tile; the clusters that get to run keep
+// their TMEM/barriers/pipeline and ask the hardware for the next not-yet-launched cluster's
+// index (clusterlaunchcontrol.try_cancel), so faster SMs simply process more tiles and the
+// tiles in flight stay adjacent in raster order (measured on B200: per-SM tile times differ
+// by up to 5 % by TPC position, which makes a static split finish at the pace of the slowest).
 //
 // Accumulators live in TMEM, double buffered (2 x BLOCK_N fp32 columns), so
 // the epilogue of tile i overlaps the main loop of tile i+1.
@@ -42,35 +58,54 @@ struct GemmParams {
   int num_kb;            // ceil(K / BLOCK_K)
   int group_m;           // tile-rasterisation group height (in tiles)
   uint32_t idesc;        // tcgen05 instruction descriptor
+  uint64_t hint_a;       // L2 eviction-priority descriptors for the A / B loads
+  uint64_t hint_b;
+  // 0: static round-robin over a grid of <= #SM CTAs.  1: the grid has one cluster per tile and
+  // running clusters obtain further tiles from the hardware (cluster launch control).
+  int dynamic;
+  // Optional trace buffer (tools only; null in production): per CTA, per tile
+  // iteration, the global-timer value at which the producer started the tile.
+  unsigned long long* trace;
 };
 
 enum class InKind : int { BF16 = 0, FP16 = 1, TF32 = 2 };
 
-template <int kCtaGroup_, int BLOCK_N_, int kElemBytes_, int kSplit_, typename OutT_>
+template <int kCtaGroup_, int BLOCK_N_, int kElemBytes_, int kSplit_, typename OutT_, bool kBKMajor_ = false,
+          int kMBlocks_ = 1>
 struct GemmConfig {
+  // 128-row accumulator blocks per CTA.
+  //   1: tile = (128 * kCtaGroup) x BLOCK_N, TMEM holds TWO accumulators (double buffered).
+  //   2: tile = (256 * kCtaGroup) x BLOCK_N, TMEM holds the tile's two halves X and Y (single
+  //      buffered); a third less L2->SM traffic per flop, and the MMA of the next tile gets a
+  //      head start on X while the epilogue is still draining Y.
+  static constexpr int kMBlocks = kMBlocks_;
   using OutT = OutT_;
+  // false: B is K x N row-major (MN-major operand, transposed by the tensor core).
+  // true:  B is given as B^T, N x K row-major (K-major operand, same layout as A).
+  static constexpr bool kBKMajor = kBKMajor_;
   static constexpr int kCtaGroup = kCtaGroup_;
   static constexpr int BLOCK_N = BLOCK_N_;
   static constexpr int kElemBytes = kElemBytes_;
   static constexpr int kSplit = kSplit_;
   static constexpr bool kTf32 = (kElemBytes_ == 4);
 
-  static constexpr int CTA_M = 128;                 // accumulator rows per CTA (TMEM lanes)
+  static constexpr int CTA_M = 128 * kMBlocks_;     // rows per CTA (kMBlocks_ x 128 TMEM lanes)
   static constexpr int TILE_M = CTA_M * kCtaGroup;  // rows per cluster tile
   static constexpr int BLOCK_K = 128 / kElemBytes;  // one 128-byte swizzle row of K
   static constexpr int UMMA_K = 32 / kElemBytes;    // K per tcgen05.mma
   static constexpr int K_STEPS = BLOCK_K / UMMA_K;  // 4
   static constexpr int LOAD_N = BLOCK_N / kCtaGroup;  // B columns this CTA loads
   static constexpr int N_ATOM = 128 / kElemBytes;     // columns in one 128-byte chunk
-  static constexpr int B_CHUNKS = LOAD_N / N_ATOM;
+  static constexpr int B_CHUNKS = kBKMajor_ ? 1 : LOAD_N / N_ATOM;
 
   static constexpr int A_BYTES = CTA_M * 128;          // 16 KB
-  static constexpr int B_CHUNK_BYTES = BLOCK_K * 128;  // BLOCK_K rows of 128 B
+  static constexpr int B_CHUNK_BYTES = (kBKMajor_ ? LOAD_N : BLOCK_K) * 128;  // rows of 128 B
   static constexpr int B_BYTES = B_CHUNKS * B_CHUNK_BYTES;
   static constexpr int STAGE_BYTES = kSplit * (A_BYTES + B_BYTES);
 
   static constexpr int kEpiWarps = 4;
-  static constexpr int kThreads = 32 * (2 + kEpiWarps);
+  static constexpr int kThreads = 32 * (3 + kEpiWarps);  // + TMA, MMA and scheduler warps
+  static constexpr int kClcSlots = 3;                    // ring of cluster-launch-control responses
   static constexpr int OUT_COLS = 128 / (int)sizeof(OutT);  // columns per 128-byte output chunk
   static constexpr int OUT_CHUNKS = BLOCK_N / OUT_COLS;
   static constexpr int OUT_BUF_BYTES = 32 * 128;  // 32 rows x 128 B, per warp
@@ -81,7 +116,10 @@ struct GemmConfig {
   static constexpr int kStages = (SMEM_LIMIT - 1024 /*align slack*/ - BAR_BYTES - OUT_BYTES) / STAGE_BYTES;
   static constexpr int SMEM_BYTES = 1024 + BAR_BYTES + kStages * STAGE_BYTES + OUT_BYTES;
 
-  static constexpr int TMEM_COLS = 2 * BLOCK_N;  // two accumulators
+  static constexpr int TMEM_COLS = 2 * BLOCK_N;  // two accumulators (two buffers, or X and Y)
+  static constexpr int kStagger = 2;             // k-blocks of head start for X when kMBlocks == 2
+  static_assert(kMBlocks_ == 1 || kMBlocks_ == 2, "one or two accumulator blocks per CTA");
+  static_assert(kMBlocks_ == 1 || kStagger < kStages, "head start must leave a free stage");
   static_assert(TMEM_COLS == 512 || TMEM_COLS == 256 || TMEM_COLS == 128 || TMEM_COLS == 64, "pow2 TMEM");
   static_assert(kStages >= 2, "pipeline too shallow");
   static_assert(LOAD_N % N_ATOM == 0, "B half must be whole 128-byte chunks");
@@ -102,14 +140,14 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 
 // Host+device: instruction descriptor for kind::f16 / kind::tf32, fp32 accumulate,
 // A K-major, B MN-major.
-__host__ __device__ inline uint32_t make_idesc(InKind kind, int umma_m, int umma_n) {
+__host__ __device__ inline uint32_t make_idesc(InKind kind, int umma_m, int umma_n, bool b_k_major = false) {
   uint32_t fmt = (kind == InKind::FP16) ? 0u : (kind == InKind::BF16 ? 1u : 2u);
   uint32_t d = 0;
   d |= 1u << 4;                          // D format: F32
   d |= fmt << 7;                         // A format
   d |= fmt << 10;                        // B format
   d |= 0u << 15;                         // A major: K
-  d |= 1u << 16;                         // B major: MN
+  d |= (b_k_major ? 0u : 1u) << 16;      // B major: MN unless B^T was supplied
   d |= (uint32_t)(umma_n >> 3) << 17;    // N / 8
   d |= (uint32_t)(umma_m >> 4) << 24;    // M / 16
   return d;
@@ -159,6 +197,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const uint32_t tfull_bar = base + 16u * kStages;               // 2 x 8 B
   const uint32_t tempty_bar = base + 16u * kStages + 16u;        // 2 x 8 B
   const uint32_t tmem_slot = base + 16u * kStages + 32u;         // 4 B
+  const uint32_t clc_full = base + 512u;                         // kClcSlots x 8 B
+  const uint32_t clc_empty = base + 512u + 32u;                  // kClcSlots x 8 B
+  const uint32_t clc_resp = base + 512u + 64u;                   // kClcSlots x 16 B
   const uint32_t tiles = base + Cfg::BAR_BYTES;                  // operand ring
   const uint32_t out_stage = tiles + kStages * Cfg::STAGE_BYTES;  // epilogue staging
 
@@ -179,6 +220,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         mbar_init(tfull_bar + 8u * a, 1);
         mbar_init(tempty_bar + 8u * a, G * Cfg::kEpiWarps);
       }
+      // Every role that walks the tile sequence consumes each response: in the leader CTA the
+      // producer, the MMA issuer, the scheduler itself and the epilogue warps; in the peer the
+      // producer and the epilogue warps.
+      constexpr uint32_t kClcConsumers = (3 + Cfg::kEpiWarps) + (G == 2 ? 1 + Cfg::kEpiWarps : 0);
+      for (int c = 0; c < Cfg::kClcSlots; ++c) {
+        mbar_init(clc_full + 8u * c, 1);
+        mbar_init(clc_empty + 8u * c, kClcConsumers);
+      }
       fence_mbar_init();
       prefetch_tensormap(&tmA);
       prefetch_tensormap(&tmB);
@@ -198,17 +247,58 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_addr));
 
+  // ---- tile sequence -------------------------------------------------------
+  // Every role walks the same sequence of tiles: its cluster's own index first, then either
+  // +num_clusters (static) or whatever the scheduler warp obtained from the hardware (dynamic;
+  // responses are consumed in order from a small ring, one slot per tile).
+  struct TileSeq {
+    int tile;
+    int slot;
+    uint32_t phase;
+  };
+  const uint32_t clc_empty_leader = (G == 2) ? mapa(clc_empty, 0) : clc_empty;
+  // kWarp: called by all 32 lanes of a warp (one lane releases the slot); else by a single thread.
+  auto next_tile = [&](TileSeq& q, bool warp_collective) -> bool {
+    if (!p.dynamic) {
+      q.tile += num_clusters;
+      return q.tile < p.num_tiles;
+    }
+    mbar_wait(clc_full + 8u * q.slot, q.phase);
+    uint32_t ctaid_x;
+    const bool ok = clc_query(clc_resp + 16u * q.slot, ctaid_x);
+    fence_proxy_async_smem();  // our read is ordered before the slot's next asynchronous overwrite
+    if (warp_collective) __syncwarp();
+    if (!warp_collective || lane == 0) {
+      if constexpr (G == 2) mbar_arrive_cluster(clc_empty_leader + 8u * q.slot);
+      else mbar_arrive(clc_empty + 8u * q.slot);
+    }
+    if (++q.slot == Cfg::kClcSlots) { q.slot = 0; q.phase ^= 1u; }
+    q.tile = (int)(ctaid_x / G);
+    return ok;
+  };
+
   if (warp == 0) {
     // ============================ TMA producer ============================
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      // Barrier that collects this stage's bytes: the leader CTA's.
-      for (int tile = cluster_id; tile < p.num_tiles; tile += num_clusters) {
+      TileSeq q{cluster_id, 0, 0u};
+      int iter = 0;
+      for (bool more = q.tile < p.num_tiles; more; more = next_tile(q, false), ++iter) {
+        const int tile = q.tile;
         int b, m_blk, n_blk;
         decode_tile(p, tile, b, m_blk, n_blk);
         const int m_row = m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M;
         const int n_col = n_blk * Cfg::BLOCK_N + (int)cta_rank * Cfg::LOAD_N;
+        if (p.trace) {  // row 0: SM id of each CTA; row 1 + i: start time of its i-th tile
+          unsigned long long now;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+          uint32_t smid;
+          asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+          // indexed by SM (not by block): with dynamic scheduling the grid is one cluster per tile
+          p.trace[(size_t)(1 + iter) * 256 + smid] = now;
+          if (iter == 0) p.trace[smid] = 1 + (unsigned long long)tile;
+        }
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(empty_bar + 8u * stage, phase ^ 1u);
           const uint32_t fb_local = full_bar + 8u * stage;
@@ -217,14 +307,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint32_t sA = tiles + stage * Cfg::STAGE_BYTES;
           const uint32_t sB = sA + Cfg::kSplit * Cfg::A_BYTES;
           const int k0 = kb * Cfg::BLOCK_K;
-          tma_load_3d<G>(sA, &tmA, fb, k0, m_row, b, kEvictNormal);
-          if constexpr (Cfg::kSplit == 2) tma_load_3d<G>(sA + Cfg::A_BYTES, &tmA_lo, fb, k0, m_row, b, kEvictNormal);
+          tma_load_3d<G>(sA, &tmA, fb, k0, m_row, b, p.hint_a);
+          if constexpr (Cfg::kSplit == 2) tma_load_3d<G>(sA + Cfg::A_BYTES, &tmA_lo, fb, k0, m_row, b, p.hint_a);
+          if constexpr (Cfg::kBKMajor) {
+            tma_load_3d<G>(sB, &tmB, fb, k0, n_col, b, p.hint_b);
+            if constexpr (Cfg::kSplit == 2) tma_load_3d<G>(sB + Cfg::B_BYTES, &tmB_lo, fb, k0, n_col, b, p.hint_b);
+          } else {
 #pragma unroll
-          for (int c = 0; c < Cfg::B_CHUNKS; ++c) {
-            tma_load_3d<G>(sB + c * Cfg::B_CHUNK_BYTES, &tmB, fb, n_col + c * Cfg::N_ATOM, k0, b, kEvictNormal);
-            if constexpr (Cfg::kSplit == 2)
-              tma_load_3d<G>(sB + Cfg::B_BYTES + c * Cfg::B_CHUNK_BYTES, &tmB_lo, fb, n_col + c * Cfg::N_ATOM, k0, b,
-                             kEvictNormal);
+            for (int c = 0; c < Cfg::B_CHUNKS; ++c) {
+              tma_load_3d<G>(sB + c * Cfg::B_CHUNK_BYTES, &tmB, fb, n_col + c * Cfg::N_ATOM, k0, b, p.hint_b);
+              if constexpr (Cfg::kSplit == 2)
+                tma_load_3d<G>(sB + Cfg::B_BYTES + c * Cfg::B_CHUNK_BYTES, &tmB_lo, fb, n_col + c * Cfg::N_ATOM, k0, b,
+                               p.hint_b);
+            }
           }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
@@ -244,41 +339,101 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const uint64_t a_desc0 = make_smem_desc(tiles, 16, 1024);
       // MN-major B: 8-row K groups 1024 B apart (SBO); 128-byte column chunks
       // B_CHUNK_BYTES apart (LBO).
-      const uint64_t b_desc0 = make_smem_desc(tiles + Cfg::kSplit * Cfg::A_BYTES, Cfg::B_CHUNK_BYTES, 1024);
+      // (K-major B^T: described exactly like A.)
+      const uint64_t b_desc0 = Cfg::kBKMajor ? make_smem_desc(tiles + Cfg::kSplit * Cfg::A_BYTES, 16, 1024)
+                                             : make_smem_desc(tiles + Cfg::kSplit * Cfg::A_BYTES, Cfg::B_CHUNK_BYTES, 1024);
       constexpr uint32_t A_KSTEP = (Cfg::UMMA_K * Cfg::kElemBytes) >> 4;  // 32 B along the swizzled row
-      constexpr uint32_t B_KSTEP = (Cfg::UMMA_K * 128) >> 4;              // UMMA_K rows of 128 B
+      constexpr uint32_t B_KSTEP = Cfg::kBKMajor ? A_KSTEP : ((Cfg::UMMA_K * 128) >> 4);  // or UMMA_K rows of 128 B
+      constexpr uint32_t A_MBLOCK = (128 * 128) >> 4;                     // next 128 rows of A in the stage
+
+      // All MMAs of one k-block for accumulator block `mb` (rows mb*128.. of this CTA's A slab).
+      auto issue_kblock = [&](int stage, int mb, uint32_t d_tmem, bool first_kb) {
+        const uint32_t soff = (uint32_t)(stage * Cfg::STAGE_BYTES) >> 4;
+        const uint64_t a_hi = a_desc0 + soff + (uint32_t)mb * A_MBLOCK;
+        const uint64_t b_hi = b_desc0 + soff;
+#pragma unroll
+        for (int k = 0; k < Cfg::K_STEPS; ++k) {
+          const uint32_t acc_in = (first_kb && k == 0) ? 0u : 1u;
+          if constexpr (Cfg::kSplit == 2) {
+            const uint64_t a_lo = a_hi + (Cfg::A_BYTES >> 4);
+            const uint64_t b_lo = b_hi + (Cfg::B_BYTES >> 4);
+            umma<G, Cfg::kTf32>(d_tmem, a_lo + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, acc_in);
+            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_lo + k * B_KSTEP, p.idesc, 1u);
+            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, 1u);
+          } else {
+            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, acc_in);
+          }
+        }
+      };
+
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = cluster_id; tile < p.num_tiles; tile += num_clusters) {
-        mbar_wait<true>(tempty_bar + 8u * acc, acc_phase ^ 1u);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::BLOCK_N);
-        for (int kb = 0; kb < p.num_kb; ++kb) {
-          mbar_wait(full_bar + 8u * stage, phase);
+      TileSeq q{cluster_id, 0, 0u};
+      for (bool more = q.tile < p.num_tiles; more; more = next_tile(q, false)) {
+        if constexpr (Cfg::kMBlocks == 1) {
+          mbar_wait<true>(tempty_bar + 8u * acc, acc_phase ^ 1u);
           tc_fence_after();
-          const uint32_t soff = (uint32_t)(stage * Cfg::STAGE_BYTES) >> 4;
-          const uint64_t a_hi = a_desc0 + soff;
-          const uint64_t b_hi = b_desc0 + soff;
-#pragma unroll
-          for (int k = 0; k < Cfg::K_STEPS; ++k) {
-            const uint32_t first = (kb | k) != 0;
-            if constexpr (Cfg::kSplit == 2) {
-              const uint64_t a_lo = a_hi + (Cfg::A_BYTES >> 4);
-              const uint64_t b_lo = b_hi + (Cfg::B_BYTES >> 4);
-              umma<G, Cfg::kTf32>(d_tmem, a_lo + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, first);
-              umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_lo + k * B_KSTEP, p.idesc, 1u);
-              umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, 1u);
-            } else {
-              umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, first);
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::BLOCK_N);
+          for (int kb = 0; kb < p.num_kb; ++kb) {
+            mbar_wait(full_bar + 8u * stage, phase);
+            tc_fence_after();
+            issue_kblock(stage, 0, d_tmem, kb == 0);
+            umma_commit<G>(empty_bar + 8u * stage, kPairMask);  // slot free once these MMAs retire
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          }
+          umma_commit<G>(tfull_bar + 8u * acc, kPairMask);  // accumulator complete
+          if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+        } else {
+          const uint32_t dX = tmem_base, dY = tmem_base + (uint32_t)Cfg::BLOCK_N;
+          const int head = p.num_kb < Cfg::kStagger ? p.num_kb : Cfg::kStagger;
+          // X has been drained: start on it while the epilogue still reads Y.
+          mbar_wait<true>(tempty_bar, acc_phase ^ 1u);
+          tc_fence_after();
+          {
+            int s = stage;
+            uint32_t ph = phase;
+            for (int kb = 0; kb < head; ++kb) {
+              mbar_wait(full_bar + 8u * s, ph);
+              tc_fence_after();
+              issue_kblock(s, 0, dX, kb == 0);
+              if (++s == kStages) { s = 0; ph ^= 1u; }
             }
           }
-          umma_commit<G>(empty_bar + 8u * stage, kPairMask);  // slot free once these MMAs retire
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          mbar_wait<true>(tempty_bar + 8u, acc_phase ^ 1u);
+          tc_fence_after();
+          for (int kb = 0; kb < head; ++kb) {  // Y catches up on the same stages, then they are released
+            issue_kblock(stage, 1, dY, kb == 0);
+            umma_commit<G>(empty_bar + 8u * stage, kPairMask);
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          }
+          for (int kb = head; kb < p.num_kb; ++kb) {
+            mbar_wait(full_bar + 8u * stage, phase);
+            tc_fence_after();
+            issue_kblock(stage, 0, dX, false);
+            issue_kblock(stage, 1, dY, false);
+            umma_commit<G>(empty_bar + 8u * stage, kPairMask);
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          }
+          umma_commit<G>(tfull_bar, kPairMask);  // X and Y complete
+          acc_phase ^= 1u;
         }
-        umma_commit<G>(tfull_bar + 8u * acc, kPairMask);  // accumulator complete
-        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2 + Cfg::kEpiWarps) {
+    // ============================== scheduler =============================
+    // Leader CTA only: one request at a time (a request may only follow a successful one),
+    // up to kClcSlots tiles ahead of the slowest consumer.
+    if (p.dynamic && cta_rank == 0 && elect_one()) {
+      TileSeq q{0, 0, 0u};
+      for (;;) {
+        mbar_wait<true>(clc_empty + 8u * q.slot, q.phase ^ 1u);
+        for (uint32_t c = 0; c < (uint32_t)G; ++c)
+          mbar_arrive_expect_tx_cluster(G == 2 ? mapa(clc_full + 8u * q.slot, c) : clc_full + 8u * q.slot, 16u);
+        clc_try_cancel(clc_resp + 16u * q.slot, clc_full + 8u * q.slot);
+        if (!next_tile(q, false)) break;  // consumes its own copy of the response
       }
     }
     __syncwarp();
@@ -289,17 +444,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int ew = warp - 2;       // staging-buffer owner index
     const uint32_t my_stage = out_stage + (uint32_t)ew * 2u * Cfg::OUT_BUF_BYTES;
     const uint32_t tempty_leader = (G == 2) ? mapa(tempty_bar, 0) : tempty_bar;
-    int acc = 0;
-    uint32_t acc_phase = 0;
     uint32_t buf = 0;
-    for (int tile = cluster_id; tile < p.num_tiles; tile += num_clusters) {
-      int b, m_blk, n_blk;
-      decode_tile(p, tile, b, m_blk, n_blk);
-      const int row0 = m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M + quarter * 32;
-      const int col0 = n_blk * Cfg::BLOCK_N;
-      mbar_wait(tfull_bar + 8u * acc, acc_phase);
-      tc_fence_after();
-      const uint32_t t_acc = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * Cfg::BLOCK_N);
+
+    // Move this warp's 32 rows of one accumulator (BLOCK_N columns at t_acc) to C, 128 bytes
+    // per row at a time; hand the accumulator back (slot) as soon as it has been read.
+    auto drain = [&](uint32_t t_acc, int row0, int col0, int b, int slot) {
 #pragma unroll 1
       for (int c = 0; c < Cfg::OUT_CHUNKS; ++c) {
         const uint32_t sbuf = my_stage + buf * Cfg::OUT_BUF_BYTES;
@@ -334,12 +483,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), v0[4 * j + 0], v0[4 * j + 1], v0[4 * j + 2], v0[4 * j + 3]);
         }
         if (c == Cfg::OUT_CHUNKS - 1) {
-          // all of this warp's TMEM reads for the tile are done: hand the accumulator back
+          // all of this warp's TMEM reads of the accumulator are done: hand it back
           tc_fence_before();
           __syncwarp();
           if (lane == 0) {
-            if constexpr (G == 2) mbar_arrive_cluster(tempty_leader + 8u * acc);
-            else mbar_arrive(tempty_bar + 8u * acc);
+            if constexpr (G == 2) mbar_arrive_cluster(tempty_leader + 8u * slot);
+            else mbar_arrive(tempty_bar + 8u * slot);
           }
         }
         fence_proxy_async_smem();
@@ -350,7 +499,29 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         buf ^= 1u;
       }
-      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    };
+
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    TileSeq q{cluster_id, 0, 0u};
+    for (bool more = q.tile < p.num_tiles; more; more = next_tile(q, true)) {
+      int b, m_blk, n_blk;
+      decode_tile(p, q.tile, b, m_blk, n_blk);
+      const int row0 = m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M + quarter * 32;
+      const int col0 = n_blk * Cfg::BLOCK_N;
+      const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+      if constexpr (Cfg::kMBlocks == 1) {
+        mbar_wait(tfull_bar + 8u * acc, acc_phase);
+        tc_fence_after();
+        drain(lane_base + (uint32_t)(acc * Cfg::BLOCK_N), row0, col0, b, acc);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      } else {
+        mbar_wait(tfull_bar, acc_phase);
+        tc_fence_after();
+        drain(lane_base, row0, col0, b, 0);                                    // X: rows 0..127 of the slab
+        drain(lane_base + (uint32_t)Cfg::BLOCK_N, row0 + 128, col0, b, 1);     // Y: rows 128..255
+        acc_phase ^= 1u;
+      }
     }
     if (lane == 0) tma_store_wait<0>();
     __syncwarp();
@@ -388,6 +559,47 @@ __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict
     const int64_t o = (b * rows + r) * cols + c4 * 4;  // packed output, ld == cols
     *reinterpret_cast<float4*>(hi + o) = make_float4(h[0], h[1], h[2], h[3]);
     *reinterpret_cast<float4*>(lo + o) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+// Same split for B, written TRANSPOSED: x is rows x cols (K x N, leading
+// dimension ld); hi/lo are cols x rows (N x K, packed).  32 x 32 tiles go
+// through shared memory so that both the read and the write are coalesced.
+__global__ void split_tf32_transpose_kernel(const float* __restrict__ x, float* __restrict__ hi,
+                                            float* __restrict__ lo, int64_t rows, int64_t cols, int64_t ld,
+                                            int64_t batch, int64_t stride) {
+  __shared__ float th[32][33];
+  __shared__ float tl[32][33];
+  const int64_t tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
+  const int64_t total = batch * tiles_r * tiles_c;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8 threads
+  for (int64_t t = blockIdx.x; t < total; t += gridDim.x) {
+    const int64_t tc = t % tiles_c;
+    const int64_t tr = (t / tiles_c) % tiles_r;
+    const int64_t b = t / (tiles_c * tiles_r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t r = tr * 32 + ty + 8 * i, c = tc * 32 + tx;
+      float v = (r < rows && c < cols) ? x[b * stride + r * ld + c] : 0.f;
+      uint32_t hb, lb;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(v));
+      const float h = __uint_as_float(hb);
+      const float rem = v - h;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(rem));
+      th[ty + 8 * i][tx] = h;
+      tl[ty + 8 * i][tx] = __uint_as_float(lb);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t c = tc * 32 + ty + 8 * i, r = tr * 32 + tx;  // output row = input column
+      if (c < cols && r < rows) {
+        const int64_t o = (b * cols + c) * rows + r;
+        hi[o] = th[tx][ty + 8 * i];
+        lo[o] = tl[tx][ty + 8 * i];
+      }
+    }
+    __syncthreads();
   }
 }
 

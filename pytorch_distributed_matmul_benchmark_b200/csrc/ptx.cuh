@@ -6,6 +6,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdio>
+
 namespace b2mm {
 namespace ptx {
 
@@ -66,6 +68,11 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 // Arrive on a barrier addressed in the cluster window (own or peer CTA).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr)
+               : "memory");
+}
+// expect_tx + arrive on a barrier addressed in the cluster window (own or peer CTA).
+__device__ __forceinline__ void mbar_arrive_expect_tx_cluster(uint32_t bar_cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(bar_cluster_addr), "r"(bytes)
                : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
@@ -188,6 +195,36 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
+
+// ------------------------------------------------- cluster launch control
+// Ask the hardware to cancel the launch of a not-yet-started cluster of this grid and hand
+// its block index to us instead (dynamic persistent scheduling).  The 16-byte response lands
+// at `resp_smem` in EVERY CTA of this cluster and completes 16 tx-bytes on the mbarrier at
+// offset `mbar` in each of them.
+__device__ __forceinline__ void clc_try_cancel(uint32_t resp_smem, uint32_t mbar) {
+  asm volatile(
+      "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 [%0], [%1];"
+      ::"r"(resp_smem), "r"(mbar)
+      : "memory");
+}
+// Decode a response: returns true and the first CTA's blockIdx.x if a cluster was obtained.
+__device__ __forceinline__ bool clc_query(uint32_t resp_smem, uint32_t& ctaid_x) {
+  uint32_t valid, x = 0;
+  asm volatile(
+      "{\n"
+      ".reg .pred p1;\n"
+      ".reg .b128 r;\n"
+      "ld.shared.b128 r, [%2];\n"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n"
+      "selp.u32 %0, 1, 0, p1;\n"
+      "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%1, _, _, _}, r;\n"
+      "}\n"
+      : "=r"(valid), "+r"(x)
+      : "r"(resp_smem)
+      : "memory");
+  ctaid_x = x;
+  return valid != 0;
+}
 
 // ----------------------------------------------------------------- tcgen05
 template <int kCtaGroup>

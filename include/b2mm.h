@@ -116,7 +116,9 @@ B2MM_API int b2mm_gemm(const void* A, const void* B, void* C,
  * the rendezvous matmul_scaling_benchmark.py:15-24 already performs. */
 B2MM_API int b2mm_comm_unique_id(void* id_out_128_bytes);
 
-/* Collective over all `world` ranks.  The current CUDA device is the rank's. */
+/* Collective over all `world` ranks.  The current CUDA device is the rank's.
+ * Stands where dist.init_process_group('nccl') creates the payload communicator
+ * (matmul_scaling_benchmark.py:19). */
 B2MM_API int b2mm_comm_init(const void* id_128_bytes, int rank, int world, void** comm_out);
 
 /* Replaces dist.destroy_process_group() for this communicator
@@ -149,9 +151,11 @@ B2MM_API int b2mm_gemm_allgather_overlap(void* comm,
                                 b2mm_stream_t compute, b2mm_stream_t comm_stream);
 
 /*
- * batch_parallel with the reduction pipelined behind compute: each local
- * batch element (or row panel, when local batch is 1) is all-reduced on
- * `comm_stream` as soon as its GEMM has finished on `compute`.
+ * batch_parallel (matmul_scaling_benchmark.py:142 bmm + :150 all_reduce) with the
+ * reduction pipelined behind compute, the double-buffered idea of
+ * backup/matmul_overlap_benchmark.py:93-180: each local batch element is cut into
+ * `n_panels` row panels; each panel is all-reduced on `comm_stream` as soon as
+ * its GEMM has finished on `compute`.  A, B, C are (local_batch, N, N) contiguous.
  */
 B2MM_API int b2mm_gemm_allreduce_overlap(void* comm,
                                 const void* A, const void* B, void* C,

@@ -243,7 +243,8 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
     count_launch(2);
     o.A = a_hi; o.A_lo = a_lo; o.lda = K; o.sA = M * K;
     o.B = b_hi; o.B_lo = b_lo; o.ldb = K; o.sB = K * N;  // B^T: N x K, packed
-    return launch_cfg<GemmConfig<2, 256, 4, 2, float, /*kBKMajor=*/true>>(o, max_sms, stream);
+    // 256 x 128 tiles, tensor-core accumulation in chunks of 8 k-blocks (K = 256), fp32 register carry.
+    return launch_cfg<GemmConfig<2, 128, 4, 2, float, /*kBKMajor=*/true, /*kMBlocks=*/1, /*kChunkKB=*/8>>(o, max_sms, stream);
   }
 
   int block_n = env_int("B2MM_BLOCK_N", 0);

@@ -39,10 +39,12 @@
 // Accumulators live in TMEM, double buffered (2 x BLOCK_N fp32 columns), so
 // the epilogue of tile i overlaps the main loop of tile i+1.
 //
-// kSplit == 2 is the fp32 path (3xTF32): A and B each arrive as a (hi, lo)
-// pair of TF32-exact fp32 arrays and every k-step issues
+// kSplit == 2 is the fp32 path (3xTF32): A and B^T each arrive as a (hi, lo)
+// pair of TF32-exact fp32 arrays (written by the split kernels at the end of
+// this file) and every k-step issues
 //   acc += Alo*Bhi;  acc += Ahi*Blo;  acc += Ahi*Bhi
-// with kind::tf32.
+// with kind::tf32; kChunkKB bounds how long the tensor core accumulates before
+// the sum is carried on in fp32 registers.
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -71,8 +73,14 @@ struct GemmParams {
 enum class InKind : int { BF16 = 0, FP16 = 1, TF32 = 2 };
 
 template <int kCtaGroup_, int BLOCK_N_, int kElemBytes_, int kSplit_, typename OutT_, bool kBKMajor_ = false,
-          int kMBlocks_ = 1>
+          int kMBlocks_ = 1, int kChunkKB_ = 0>
 struct GemmConfig {
+  // > 0: the tensor core accumulates only kChunkKB_ k-blocks at a time in TMEM; the epilogue warps
+  // add each finished chunk into fp32 REGISTERS (round-to-nearest) and store at the end of the
+  // tile.  The tensor core's fp32 accumulator truncates on every add, a bias that grows linearly
+  // with the accumulation length (measured: 3e-4 relative at K = 16384); short chunks keep it at
+  // the level of K = chunk.  Used by the fp32 (3xTF32) path; needs BLOCK_N <= 128 and kMBlocks == 1.
+  static constexpr int kChunkKB = kChunkKB_;
   // 128-row accumulator blocks per CTA.
   //   1: tile = (128 * kCtaGroup) x BLOCK_N, TMEM holds TWO accumulators (double buffered).
   //   2: tile = (256 * kCtaGroup) x BLOCK_N, TMEM holds the tile's two halves X and Y (single
@@ -119,6 +127,8 @@ struct GemmConfig {
   static constexpr int TMEM_COLS = 2 * BLOCK_N;  // two accumulators (two buffers, or X and Y)
   static constexpr int kStagger = 2;             // k-blocks of head start for X when kMBlocks == 2
   static_assert(kMBlocks_ == 1 || kMBlocks_ == 2, "one or two accumulator blocks per CTA");
+  static_assert(kChunkKB_ == 0 || (kMBlocks_ == 1 && BLOCK_N_ <= 128 && sizeof(OutT_) == 4),
+                "register accumulation: one 128-row block, <= 128 fp32 columns per thread");
   static_assert(kMBlocks_ == 1 || kStagger < kStages, "head start must leave a free stage");
   static_assert(TMEM_COLS == 512 || TMEM_COLS == 256 || TMEM_COLS == 128 || TMEM_COLS == 64, "pow2 TMEM");
   static_assert(kStages >= 2, "pipeline too shallow");
@@ -373,18 +383,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       TileSeq q{cluster_id, 0, 0u};
       for (bool more = q.tile < p.num_tiles; more; more = next_tile(q, false)) {
         if constexpr (Cfg::kMBlocks == 1) {
-          mbar_wait<true>(tempty_bar + 8u * acc, acc_phase ^ 1u);
-          tc_fence_after();
-          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::BLOCK_N);
+          // One accumulator per chunk of k-blocks (the whole K unless kChunkKB is set).
+          const int chunk_kb = Cfg::kChunkKB > 0 ? Cfg::kChunkKB : p.num_kb;
+          int in_chunk = 0;
           for (int kb = 0; kb < p.num_kb; ++kb) {
+            if (in_chunk == 0) {
+              mbar_wait<true>(tempty_bar + 8u * acc, acc_phase ^ 1u);
+              tc_fence_after();
+            }
             mbar_wait(full_bar + 8u * stage, phase);
             tc_fence_after();
-            issue_kblock(stage, 0, d_tmem, kb == 0);
+            issue_kblock(stage, 0, tmem_base + (uint32_t)(acc * Cfg::BLOCK_N), in_chunk == 0);
             umma_commit<G>(empty_bar + 8u * stage, kPairMask);  // slot free once these MMAs retire
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
+            if (++in_chunk == chunk_kb || kb == p.num_kb - 1) {
+              umma_commit<G>(tfull_bar + 8u * acc, kPairMask);  // accumulator (chunk) complete
+              if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+              in_chunk = 0;
+            }
           }
-          umma_commit<G>(tfull_bar + 8u * acc, kPairMask);  // accumulator complete
-          if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
         } else {
           const uint32_t dX = tmem_base, dY = tmem_base + (uint32_t)Cfg::BLOCK_N;
           const int head = p.num_kb < Cfg::kStagger ? p.num_kb : Cfg::kStagger;
@@ -510,7 +527,55 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int row0 = m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M + quarter * 32;
       const int col0 = n_blk * Cfg::BLOCK_N;
       const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
-      if constexpr (Cfg::kMBlocks == 1) {
+      if constexpr (Cfg::kChunkKB > 0) {
+        // Register accumulation: this thread owns one row of the tile, BLOCK_N fp32 sums.
+        float sum[Cfg::BLOCK_N];
+#pragma unroll
+        for (int j = 0; j < Cfg::BLOCK_N; ++j) sum[j] = 0.f;
+        const int n_chunks = (p.num_kb + Cfg::kChunkKB - 1) / Cfg::kChunkKB;
+#pragma unroll 1
+        for (int ch = 0; ch < n_chunks; ++ch) {
+          mbar_wait(tfull_bar + 8u * acc, acc_phase);
+          tc_fence_after();
+          const uint32_t t_acc = lane_base + (uint32_t)(acc * Cfg::BLOCK_N);
+#pragma unroll
+          for (int c = 0; c < Cfg::BLOCK_N / 32; ++c) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_acc + (uint32_t)(c * 32), v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              sum[c * 32 + j] = __fadd_rn(sum[c * 32 + j], __uint_as_float(v[j]));
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if constexpr (G == 2) mbar_arrive_cluster(tempty_leader + 8u * acc);
+            else mbar_arrive(tempty_bar + 8u * acc);
+          }
+          if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+        }
+#pragma unroll
+        for (int c = 0; c < Cfg::OUT_CHUNKS; ++c) {
+          const uint32_t sbuf = my_stage + buf * Cfg::OUT_BUF_BYTES;
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          const uint32_t srow = sbuf + (uint32_t)lane * 128u;
+          const uint32_t sw = (uint32_t)(lane & 7);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), __float_as_uint(sum[c * 32 + 4 * j + 0]),
+                         __float_as_uint(sum[c * 32 + 4 * j + 1]), __float_as_uint(sum[c * 32 + 4 * j + 2]),
+                         __float_as_uint(sum[c * 32 + 4 * j + 3]));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_3d(&tmC, sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
+            tma_store_commit();
+          }
+          buf ^= 1u;
+        }
+      } else if constexpr (Cfg::kMBlocks == 1) {
         mbar_wait(tfull_bar + 8u * acc, acc_phase);
         tc_fence_after();
         drain(lane_base + (uint32_t)(acc * Cfg::BLOCK_N), row0, col0, b, acc);

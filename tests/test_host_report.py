@@ -1,0 +1,120 @@
+"""Host layer parity: CLI surface and report text against what the reference itself printed
+(tests/golden/host_logic.json, captured from the reference's run_benchmarks with stub timings). CPU only."""
+import contextlib
+import io
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+from conftest import ROOT
+from pytorch_distributed_matmul_benchmark_b200 import hostlib
+from pytorch_distributed_matmul_benchmark_b200 import matmul_benchmark as mb
+from pytorch_distributed_matmul_benchmark_b200 import matmul_scaling_benchmark as ms
+
+
+def _capture(fn):
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        fn()
+    return buf.getvalue()
+
+
+def _normalise(text: str) -> str:
+    # the one deliberate difference: the efficiency line names B200 and its peak instead of "RTX 6000 Ada"
+    return re.sub(r"  - GPU Efficiency: .*\n", "  - GPU Efficiency: <peak-specific>\n", text)
+
+
+def test_cli_defaults_match_reference(host_logic):
+    a = mb.build_parser().parse_args([])
+    assert [0, 1, a.sizes, str(hostlib.DTYPE_MAP[a.dtype]), a.iterations, a.warmup] == host_logic["cli_mb_default"]
+    a = ms.build_parser().parse_args([])
+    assert [0, 1, a.sizes, str(hostlib.DTYPE_MAP[a.dtype]), a.mode, a.iterations, a.warmup] == host_logic["cli_ms_default"]
+    a = ms.build_parser().parse_args(["--sizes", "512", "1024", "--mode", "matrix_parallel", "--dtype", "float16",
+                                      "--iterations", "7", "--warmup", "2"])
+    assert [0, 1, a.sizes, str(hostlib.DTYPE_MAP[a.dtype]), a.mode, a.iterations, a.warmup] == host_logic["cli_ms_custom"]
+    assert [m.value for m in ms.ScalingMode] == host_logic["modes"]
+    with pytest.raises(SystemExit):
+        ms.build_parser().parse_args(["--mode", "data_parallel"])
+    with pytest.raises(SystemExit):
+        mb.build_parser().parse_args(["--dtype", "float64"])
+
+
+def test_basic_report_text_matches_reference(host_logic):
+    t = host_logic["fake_time"]
+    stub = lambda size, dtype, device, it, wu: (t, hostlib.calculate_tflops(size, t))  # noqa: E731
+    out = _capture(lambda: mb.run_benchmarks(0, 1, [4096, 16384], torch.bfloat16, 50, 10, bench_fn=stub, device="cpu"))
+    assert _normalise(out) == _normalise(host_logic["report_mb_bf16"])
+    out = _capture(lambda: mb.run_benchmarks(0, 1, [4096], torch.float32, 50, 10, bench_fn=stub, device="cpu"))
+    assert _normalise(out) == _normalise(host_logic["report_mb_fp32"])
+    assert "% of B200 theoretical peak" in out or "B200" in out
+
+
+@pytest.mark.parametrize("mode", list(ms.ScalingMode))
+def test_scaling_report_text_matches_reference(host_logic, mode):
+    t = host_logic["fake_time"]
+    stubs = {
+        ms.ScalingMode.INDEPENDENT: lambda size: (t, hostlib.calculate_tflops(size, t, 1)),
+        ms.ScalingMode.BATCH_PARALLEL: lambda size: (t, hostlib.calculate_tflops(size, t, 4)),
+        ms.ScalingMode.MATRIX_PARALLEL: lambda size: (t, hostlib.calculate_tflops(size, t, 1)),
+    }
+    out = _capture(lambda: ms.run_benchmarks(0, 1, [4096, 16384], torch.bfloat16, mode, 50, 10, bench_fns=stubs,
+                                              device="cpu"))
+    assert out == host_logic[f"report_ms_{mode.value}"]
+
+
+def test_report_keeps_the_substrings_compare_benchmarks_greps(host_logic):
+    """backup/compare_benchmarks.py:22-26 filters stdout on these substrings."""
+    out = host_logic["report_ms_independent"]
+    for needle in ("16384x16384", "Results for", "TFLOPS"):
+        assert needle in out
+    t = host_logic["fake_time"]
+    mine = _capture(lambda: mb.run_benchmarks(0, 1, [16384], torch.bfloat16, 50, 10, device="cpu",
+                                               bench_fn=lambda *a: (t, hostlib.calculate_tflops(16384, t))))
+    for needle in ("16384x16384", "Results for", "Average time", "TFLOPS"):
+        assert needle in mine
+
+
+def test_per_size_error_net_prints_error_and_continues():
+    """matmul_benchmark.py:143-148: an exception in one size becomes an ERROR: line; the loop goes on."""
+    calls = []
+
+    def flaky(size, dtype, device, it, wu):
+        calls.append(size)
+        if size == 8192:
+            raise RuntimeError("boom")
+        return 0.001, 1.0
+
+    out = _capture(lambda: mb.run_benchmarks(0, 1, [4096, 8192, 16384], torch.bfloat16, 5, 1, bench_fn=flaky, device="cpu"))
+    assert calls == [4096, 8192, 16384]
+    assert "\n  ERROR: boom" in out and "Results for 16384x16384" in out and "Results for 8192x8192" not in out
+
+
+def test_calculate_tflops_and_split_match_reference(host_logic):
+    for n, t, v in host_logic["calculate_tflops_mb"]:
+        assert hostlib.calculate_tflops(n, t) == pytest.approx(v, rel=1e-12)
+    for n, t, k, v in host_logic["calculate_tflops_ms"]:
+        assert hostlib.calculate_tflops(n, t, k) == pytest.approx(v, rel=1e-12)
+    for N, ws, rank, s, e in host_logic["col_split"]:
+        assert hostlib.split_columns(N, ws, rank) == (s, e)
+
+
+def test_launchers_keep_the_reference_positionals():
+    """run_benchmark.sh: NUM_GPUS [DTYPE]; run_scaling_benchmark.sh: NUM_GPUS [MODE] [DTYPE] (defaults 1/bf16, 2/independent/bf16)."""
+    rb = open(os.path.join(ROOT, "run_benchmark.sh")).read()
+    rs = open(os.path.join(ROOT, "run_scaling_benchmark.sh")).read()
+    assert "NUM_GPUS=${1:-1}" in rb and "DTYPE=${2:-bfloat16}" in rb
+    assert "NUM_GPUS=${1:-2}" in rs and "MODE=${2:-independent}" in rs and "DTYPE=${3:-bfloat16}" in rs
+    for text in (rb, rs):
+        assert "--sizes 4096 8192 16384 --iterations 50 --warmup 10" in text
+        assert "torch.distributed.run" in text and "--nproc_per_node=$NUM_GPUS" in text
+    assert "--master_port=29500" in rb and "--master_port=29503" in rs
+    for script in ("run_benchmark.sh", "run_scaling_benchmark.sh"):
+        subprocess.check_call(["bash", "-n", os.path.join(ROOT, script)])
+
+
+def test_cpu_device_is_refused_by_the_product_benchmark():
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        mb.benchmark_matmul(64, torch.float32, "cpu", 1, 0)

@@ -1,0 +1,50 @@
+"""The oracle is the checker, never the product: nothing shipped may import, load or exec oracle/."""
+import os
+import re
+
+from conftest import ROOT
+
+PRODUCT_DIRS = ["pytorch_distributed_matmul_benchmark_b200", "include"]
+PRODUCT_FILES = ["matmul_benchmark.py", "matmul_scaling_benchmark.py", "run_benchmark.sh", "run_scaling_benchmark.sh"]
+PAT = re.compile(r"^\s*(from|import)\s+oracle\b|liboracle|oracle/_build|oracle\.gemm|gemm_oracle", re.M)
+
+
+def _files():
+    for d in PRODUCT_DIRS:
+        for dirpath, _, names in os.walk(os.path.join(ROOT, d)):
+            if "build" in dirpath.split(os.sep):
+                continue
+            for n in names:
+                if n.endswith((".py", ".cu", ".cuh", ".h", ".sh", "Makefile")):
+                    yield os.path.join(dirpath, n)
+    for f in PRODUCT_FILES:
+        p = os.path.join(ROOT, f)
+        if os.path.exists(p):
+            yield p
+
+
+def test_product_never_touches_the_oracle():
+    offenders = []
+    for path in _files():
+        text = open(path, errors="ignore").read()
+        if PAT.search(text):
+            offenders.append(os.path.relpath(path, ROOT))
+    assert not offenders, f"product files referencing the oracle: {offenders}"
+
+
+def test_product_has_no_library_gemm_fallback():
+    """No torch.matmul / cuBLAS on the product path (hostlib.parity_error is the --check reference, not a fallback)."""
+    bad = []
+    for path in _files():
+        if not path.endswith(".py"):
+            continue
+        rel = os.path.relpath(path, ROOT)
+        for i, line in enumerate(open(path).read().splitlines(), 1):
+            code = line.split("#")[0]
+            if re.search(r"torch\.(matmul|bmm|mm)\(|cublas", code) and not rel.endswith("hostlib.py"):
+                bad.append(f"{rel}:{i}")
+    assert not bad, bad
+    for path in _files():
+        if path.endswith((".cu", ".cuh", "Makefile")):
+            text = open(path).read().lower()
+            assert "cublas" not in text and "-lcublas" not in text, path

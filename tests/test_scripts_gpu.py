@@ -1,0 +1,59 @@
+"""The drop-in scripts end to end on the GPU (single process), and the multi-rank modes when >= 2 GPUs are present."""
+import os
+import re
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(cmd, timeout=900):
+    p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+    assert p.returncode == 0, p.stdout[-4000:] + p.stderr[-4000:]
+    return p.stdout
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_matmul_benchmark_script():
+    out = _run([sys.executable, "matmul_benchmark.py", "--sizes", "1024", "2048", "--iterations", "5", "--warmup", "2",
+                "--dtype", "bfloat16", "--check"])
+    assert "Running in single GPU mode" in out
+    assert "Results for 1024x1024:" in out and "Results for 2048x2048:" in out
+    assert out.count("-> OK") == 2 and "ERROR" not in out
+    assert re.search(r"  - TFLOPS per GPU: \d+\.\d\d", out)
+    assert "% of B200 theoretical peak" in out
+
+
+@pytest.mark.parametrize("dtype", ["float16", "float32"])
+def test_scaling_script_single_gpu_all_modes(dtype):
+    for mode in ("independent", "batch_parallel", "matrix_parallel"):
+        out = _run([sys.executable, "matmul_scaling_benchmark.py", "--sizes", "1024", "--iterations", "3", "--warmup",
+                    "1", "--dtype", dtype, "--mode", mode, "--check"])
+        assert f"  - Mode: {mode}" in out and "Results for 1024x1024:" in out
+        assert "-> OK" in out and "ERROR" not in out and "FAIL" not in out
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("mode,extra", [("independent", []), ("batch_parallel", []), ("matrix_parallel", []),
+                                        ("batch_parallel", ["--overlap", "--panels", "2"]),
+                                        ("matrix_parallel", ["--overlap", "--panels", "4"])])
+def test_scaling_script_two_gpus(mode, extra):
+    out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                "--master-addr=127.0.0.1", f"--master-port={_free_port()}", "matmul_scaling_benchmark.py", "--sizes",
+                "2048", "--iterations", "3", "--warmup", "2", "--dtype", "bfloat16", "--mode", mode, "--check"] + extra)
+    assert "Collective operations verified successfully across 2 GPUs" in out
+    assert "Results for 2048x2048:" in out and "ERROR" not in out and "FAIL" not in out
+    assert "-> OK" in out
+    if extra:
+        assert "Overlapped end-to-end:" in out

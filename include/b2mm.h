@@ -104,6 +104,38 @@ B2MM_API int b2mm_gemm(const void* A, const void* B, void* C,
               int dtype, void* workspace, size_t workspace_bytes,
               b2mm_stream_t stream);
 
+/*
+ * fp32 C = A * B (2-D, row-major, same layout rules as b2mm_gemm) for callers that must not
+ * allocate device memory.  It has no counterpart in the reference, where torch allocates freely.
+ *
+ * Who this is for: b2mm_gemm's fp32 path wants 8*(M*K + K*N) bytes of workspace from its caller.
+ * Some hosts of this library cannot provide it: a serving process that handed the whole GPU to its
+ * own memory pool at start-up (a later cudaMalloc fails, or punches holes into that pool); a
+ * latency-critical loop that cannot afford cudaMalloc's device-wide synchronisation; a thin C or
+ * ctypes caller that owns only the buffers it was handed and has no allocator to ask.  For them the
+ * scratch is a fixed array compiled into the library's device image.
+ *
+ * Limit: B2MM_NOALLOC_SCRATCH_BYTES (32 MiB) on every GPU that loads the library, held until the
+ * process exits.  A problem whose split operands need more (8*(M*K + K*N) bytes, each operand's pair
+ * rounded up to 256 bytes) is refused with B2MM_ERR_WORKSPACE and a message that names the limit;
+ * e.g. 1024 x 1024 x 1024 needs 16 MiB and fits, 2048^3 does not.
+ *
+ * Set-up: the first call on a device resolves the array's device address (once per device, with
+ * that device current).  Make that first call before any stream capture begins.
+ *
+ * Sharing: every call on a device uses the same array, and the array keeps what the previous call
+ * left in it.  Nothing has to be cleared — a call overwrites every byte it later reads — but two
+ * calls whose GPU work may overlap (different streams without an event between them) race on the
+ * scratch.  Keep them on one stream, or order them with events.
+ *
+ * Performs no cudaMalloc/cudaFree and calls no allocating library routine.
+ */
+#define B2MM_NOALLOC_SCRATCH_BYTES (32u << 20)
+B2MM_API int b2mm_gemm_fp32_noalloc(const float* A, const float* B, float* C,
+                                    int64_t M, int64_t N, int64_t K,
+                                    int64_t lda, int64_t ldb, int64_t ldc,
+                                    b2mm_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Collectives.  The communicator wraps an ncclComm_t owned by the library
  * (libnccl is dlopen'ed on first use; the same libnccl.so.2 torch loaded).

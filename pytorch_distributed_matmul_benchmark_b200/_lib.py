@@ -22,6 +22,7 @@ ERR_WORKSPACE = 5
 
 BF16, FP16, FP32 = 0, 1, 2
 UNIQUE_ID_BYTES = 128
+NOALLOC_SCRATCH_BYTES = 32 << 20
 
 # name -> (restype, argtypes); must list every symbol include/b2mm.h declares
 # (tests/test_abi.py checks the two against each other).
@@ -33,6 +34,8 @@ SIGNATURES = {
     "b2mm_gemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64, c_int]),
     "b2mm_gemm": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
                           c_int64, c_int64, c_int64, c_int64, c_int, c_void_p, c_size_t, c_void_p]),
+    "b2mm_gemm_fp32_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
+                                       c_void_p]),
     "b2mm_comm_unique_id": (c_int, [c_void_p]),
     "b2mm_comm_init": (c_int, [c_void_p, c_int, c_int, ctypes.POINTER(c_void_p)]),
     "b2mm_comm_destroy": (c_int, [c_void_p]),

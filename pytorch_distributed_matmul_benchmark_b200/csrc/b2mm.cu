@@ -276,6 +276,32 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
   }
 }
 
+// ------------------------------------------------------- fixed scratch for b2mm_gemm_fp32_noalloc
+// The hi/lo split operands of the fp32 path, for callers that cannot allocate (see include/b2mm.h).
+// One array per device image; in host code its name is only a handle, the device address comes from
+// cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B2MM_NOALLOC_SCRATCH_BYTES];
+
+// Device address of g_noalloc_scratch on the CURRENT device; resolved once per device.
+static int noalloc_scratch_address(void** out) {
+  static std::mutex mu;
+  static void* resolved[64] = {nullptr};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= 64) return fail(B2MM_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!resolved[dev]) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr)
+      return fail(B2MM_ERR_CUDA, "cudaGetSymbolAddress(noalloc scratch) on device %d: %s", dev, cudaGetErrorString(e));
+    resolved[dev] = ptr;
+  }
+  *out = resolved[dev];
+  return B2MM_OK;
+}
+
 }  // namespace b2mm
 
 extern "C" {
@@ -297,6 +323,23 @@ int b2mm_gemm(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
               void* workspace, size_t workspace_bytes, b2mm_stream_t stream) {
   return b2mm::gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, batch, strideA, strideB, strideC, dtype, workspace,
                          workspace_bytes, /*max_sms=*/0, (cudaStream_t)stream);
+}
+
+int b2mm_gemm_fp32_noalloc(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t K, int64_t lda,
+                           int64_t ldb, int64_t ldc, b2mm_stream_t stream) {
+  using namespace b2mm;
+  if (M < 0 || N < 0 || K < 0) return fail(B2MM_ERR_BAD_ARG, "negative size");
+  const size_t need = gemm_workspace_bytes(M, N, K, 1, B2MM_FP32);
+  if (need > (size_t)B2MM_NOALLOC_SCRATCH_BYTES)
+    return fail(B2MM_ERR_WORKSPACE,
+                "b2mm_gemm_fp32_noalloc: %lld x %lld x %lld needs %zu bytes of split scratch, the built-in array holds %zu "
+                "(B2MM_NOALLOC_SCRATCH_BYTES); use b2mm_gemm with caller workspace for larger problems",
+                (long long)M, (long long)N, (long long)K, need, (size_t)B2MM_NOALLOC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (int rc = noalloc_scratch_address(&scratch)) return rc;
+  // Same kernels as b2mm_gemm(dtype = fp32); the split pre-pass rewrites every scratch byte the GEMM reads.
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 1, 0, 0, 0, B2MM_FP32, scratch, (size_t)B2MM_NOALLOC_SCRATCH_BYTES,
+                   /*max_sms=*/0, (cudaStream_t)stream);
 }
 
 }  // extern "C"

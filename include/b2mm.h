@@ -167,6 +167,40 @@ B2MM_API int b2mm_all_reduce_sum(void* comm, void* buf, int64_t count, int dtype
 B2MM_API int b2mm_all_gather(void* comm, const void* send, void* recv_slabs,
                     int64_t count_per_rank, int dtype, b2mm_stream_t stream);
 
+/* Peer mapping for the fused collectives (CUDA IPC, one process per GPU on one node).  The owner of
+ * a device buffer exports a 64-byte handle plus the buffer's offset inside its allocation; the bytes
+ * travel over the existing process group; every other rank imports them with ITS device current and
+ * gets a pointer its kernels can load/store through NVLink.  No counterpart in the reference (torch's
+ * NCCL process group does the equivalent internally for dist.all_gather, matmul_scaling_benchmark.py:221).
+ * Imported mappings live until process exit. */
+#define B2MM_IPC_HANDLE_BYTES 64
+B2MM_API int b2mm_ipc_export(const void* ptr, void* handle_out_64_bytes, int64_t* offset_out);
+B2MM_API int b2mm_ipc_import(const void* handle_64_bytes, int64_t offset, void** ptr_out);
+
+/* Cross-rank barrier on `stream` (a one-word ncclAllReduce): everything enqueued on `stream` before
+ * it, on every rank, has completed before anything after it starts, on any rank.  Stands where the
+ * reference calls dist.barrier() (matmul_scaling_benchmark.py:82,129,198); required after
+ * b2mm_gemm_allgather_fused before any rank reads its slabs. */
+B2MM_API int b2mm_comm_barrier(void* comm, b2mm_stream_t stream);
+
+/*
+ * matrix_parallel as ONE kernel: C_local = A * B_local (matmul_scaling_benchmark.py:211) whose epilogue
+ * writes every finished tile straight into slab `rank` of EVERY rank's gather buffer over NVLink
+ * (TMA stores to peer-mapped memory), i.e. the all_gather of :221 overlapped with the math tile by
+ * tile, with no collective kernel and no SMs taken from the GEMM.
+ *
+ *   peer_slabs[d]: base of rank d's [world][M][n_local] buffer as mapped into THIS process (d == rank:
+ *   the local buffer; others: CUDA-IPC / peer mappings).  world <= 8.
+ *
+ * The stores of other ranks into the caller's buffer are complete only after a b2mm_comm_barrier
+ * (or any cross-rank synchronisation) that follows this call on every rank; likewise nobody may still
+ * be reading the buffers when the call starts.
+ */
+B2MM_API int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void* const* peer_slabs,
+                                       int rank, int world, int64_t M, int64_t n_local, int64_t K,
+                                       int dtype, void* workspace, size_t workspace_bytes,
+                                       b2mm_stream_t stream);
+
 /*
  * matrix_parallel with the gather pipelined behind compute
  * (after backup/matmul_overlap_benchmark.py:93-180, made race-free):

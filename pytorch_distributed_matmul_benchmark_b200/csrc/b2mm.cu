@@ -104,6 +104,8 @@ struct Operands {
   void* C;
   int64_t M, N, K, lda, ldb, ldc, batch, sA, sB, sC;
   int dtype;
+  void* const* fan_ptrs;  // fanout destinations for C (null: just C)
+  int fanout;
 };
 
 template <class Cfg>
@@ -116,7 +118,18 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   } else {
     if ((rc = make_map(&tmB, o.B, o.dtype, o.N, o.K, o.batch, o.ldb, o.sB, Cfg::N_ATOM, Cfg::BLOCK_K))) return rc;
   }
-  if ((rc = make_map(&tmC, o.C, o.dtype, o.N, o.M, o.batch, o.ldc, o.sC, Cfg::OUT_COLS, 32))) return rc;
+  static FanoutMaps fan_none;  // zero-filled; never dereferenced when fanout == 0
+  FanoutMaps fan_local;
+  const FanoutMaps* fan = &fan_none;
+  if (o.fanout > 0) {
+    for (int d = 0; d < o.fanout; ++d)
+      if ((rc = make_map(&fan_local.m[d], o.fan_ptrs[d], o.dtype, o.N, o.M, o.batch, o.ldc, o.sC, Cfg::OUT_COLS, 32))) return rc;
+    for (int d = o.fanout; d < kMaxFanout; ++d) fan_local.m[d] = fan_local.m[0];
+    fan = &fan_local;
+    tmC = fan_local.m[0];
+  } else if ((rc = make_map(&tmC, o.C, o.dtype, o.N, o.M, o.batch, o.ldc, o.sC, Cfg::OUT_COLS, 32))) {
+    return rc;
+  }
   if (Cfg::kSplit == 2) {
     if ((rc = make_map(&tmA_lo, o.A_lo, o.dtype, o.K, o.M, o.batch, o.lda, o.sA, Cfg::BLOCK_K, Cfg::CTA_M))) return rc;
     if (Cfg::kBKMajor) {
@@ -143,6 +156,7 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   p.hint_a = kHints[env_int("B2MM_HINT_A", 0) % 3];
   p.hint_b = kHints[env_int("B2MM_HINT_B", 0) % 3];
   p.trace = g_trace;
+  p.fanout = o.fanout;
   // Dynamic (hardware work-stealing) scheduling unless the caller capped the SMs.
   const char* sched = getenv("B2MM_SCHED");
   p.dynamic = (max_sms > 0 || (sched && !strcmp(sched, "static"))) ? 0 : 1;
@@ -177,7 +191,7 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmA_lo, tmB_lo, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmA_lo, tmB_lo, *fan, p);
   if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
   count_launch(1);
   return B2MM_OK;
@@ -201,8 +215,15 @@ size_t gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int 
 
 int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
               int64_t ldc, int64_t batch, int64_t sA, int64_t sB, int64_t sC, int dtype, void* workspace,
-              size_t workspace_bytes, int max_sms, cudaStream_t stream) {
+              size_t workspace_bytes, int max_sms, cudaStream_t stream, void* const* fan_ptrs, int fanout) {
   const int es = dtype_bytes(dtype);
+  if (fanout < 0 || fanout > kMaxFanout) return fail(B2MM_ERR_UNSUPPORTED, "fan-out of %d destinations (max %d)", fanout, kMaxFanout);
+  if (fanout > 0) {
+    if (!fan_ptrs) return fail(B2MM_ERR_BAD_ARG, "null destination list");
+    for (int d = 0; d < fanout; ++d)
+      if (!fan_ptrs[d] || ((uintptr_t)fan_ptrs[d] & 15)) return fail(B2MM_ERR_BAD_ARG, "destination %d is null or not 16-byte aligned", d);
+    C = fan_ptrs[0];
+  }
   if (es == 0) return fail(B2MM_ERR_BAD_ARG, "unknown dtype %d", dtype);
   if (batch < 0 || M < 0 || N < 0 || K < 0) return fail(B2MM_ERR_BAD_ARG, "negative size");
   if (batch == 0 || M == 0 || N == 0) return B2MM_OK;  // empty output: nothing to do (torch.bmm on b=0)
@@ -218,7 +239,7 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
   if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX || batch > 65535)
     return fail(B2MM_ERR_UNSUPPORTED, "dimension too large");
 
-  Operands o{A, B, nullptr, nullptr, C, M, N, K, lda, ldb, ldc, batch, sA, sB, sC, dtype};
+  Operands o{A, B, nullptr, nullptr, C, M, N, K, lda, ldb, ldc, batch, sA, sB, sC, dtype, fan_ptrs, fanout};
   const int sms = device_sm_count();
   int clusters = (max_sms > 0 && max_sms < sms ? max_sms : sms) / 2;
   if (clusters < 1) clusters = 1;
@@ -339,7 +360,7 @@ int b2mm_gemm_fp32_noalloc(const float* A, const float* B, float* C, int64_t M, 
   if (int rc = noalloc_scratch_address(&scratch)) return rc;
   // Same kernels as b2mm_gemm(dtype = fp32); the split pre-pass rewrites every scratch byte the GEMM reads.
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 1, 0, 0, 0, B2MM_FP32, scratch, (size_t)B2MM_NOALLOC_SCRATCH_BYTES,
-                   /*max_sms=*/0, (cudaStream_t)stream);
+                   /*max_sms=*/0, (cudaStream_t)stream, nullptr, 0);
 }
 
 }  // extern "C"

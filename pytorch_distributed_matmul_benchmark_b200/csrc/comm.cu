@@ -65,6 +65,7 @@ struct Comm {
   int rank = 0, world = 1;
   cudaEvent_t panel_done[kMaxPanels];
   cudaEvent_t comm_done = nullptr;
+  float* barrier_word = nullptr;  // 1 float on the device: payload of b2mm_comm_barrier
 };
 
 static int nccl_fail(const char* what, ncclResult_t r) {
@@ -122,6 +123,10 @@ int b2mm_comm_init(const void* id_bytes, int rank, int world, void** comm_out) {
       return fail(B2MM_ERR_CUDA, "cudaEventCreate failed");
     }
   cudaEventCreateWithFlags(&c->comm_done, cudaEventDisableTiming);
+  if (cudaMalloc(&c->barrier_word, 256) != cudaSuccess || cudaMemset(c->barrier_word, 0, 256) != cudaSuccess) {
+    delete c;
+    return fail(B2MM_ERR_CUDA, "cudaMalloc(barrier word) failed");
+  }
   *comm_out = c;
   return B2MM_OK;
 }
@@ -131,6 +136,7 @@ int b2mm_comm_destroy(void* comm) {
   Comm* c = (Comm*)comm;
   for (int i = 0; i < kMaxPanels; ++i) cudaEventDestroy(c->panel_done[i]);
   if (c->comm_done) cudaEventDestroy(c->comm_done);
+  if (c->barrier_word) cudaFree(c->barrier_word);
   if (c->nccl) nccl().CommDestroy(c->nccl);
   delete c;
   return B2MM_OK;
@@ -157,6 +163,93 @@ int b2mm_all_gather(void* comm, const void* send, void* recv_slabs, int64_t coun
   ncclResult_t r = nccl().AllGather(send, recv_slabs, (size_t)count_per_rank, t, c->nccl, (cudaStream_t)stream);
   if (r != ncclSuccess) return nccl_fail("ncclAllGather", r);
   return B2MM_OK;
+}
+
+// ---- CUDA IPC: make a peer rank's buffer addressable from this rank's device ----------------
+namespace {
+struct IpcEntry {
+  cudaIpcMemHandle_t h;
+  void* base;
+};
+std::mutex g_ipc_mu;
+IpcEntry g_ipc_open[64];
+int g_ipc_n = 0;
+
+using GetRangeFn = int (*)(unsigned long long*, size_t*, unsigned long long);
+GetRangeFn get_range_fn() {
+  static GetRangeFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<GetRangeFn>(p);
+  });
+  return fn;
+}
+}  // namespace
+
+int b2mm_ipc_export(const void* ptr, void* handle_out_64_bytes, int64_t* offset_out) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == B2MM_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t size");
+  if (!ptr || !handle_out_64_bytes || !offset_out) return fail(B2MM_ERR_BAD_ARG, "null argument");
+  GetRangeFn range = get_range_fn();
+  if (!range) return fail(B2MM_ERR_CUDA, "cuMemGetAddressRange not available from the driver");
+  unsigned long long base = 0;
+  size_t size = 0;
+  if (range(&base, &size, (unsigned long long)(uintptr_t)ptr) != 0) return fail(B2MM_ERR_CUDA, "cuMemGetAddressRange failed");
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base);
+  if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+  memcpy(handle_out_64_bytes, &h, sizeof(h));
+  *offset_out = (int64_t)((unsigned long long)(uintptr_t)ptr - base);
+  return B2MM_OK;
+}
+
+int b2mm_ipc_import(const void* handle_64_bytes, int64_t offset, void** ptr_out) {
+  if (!handle_64_bytes || !ptr_out || offset < 0) return fail(B2MM_ERR_BAD_ARG, "bad ipc_import argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle_64_bytes, sizeof(h));
+  std::lock_guard<std::mutex> lock(g_ipc_mu);
+  for (int i = 0; i < g_ipc_n; ++i)  // an allocation can be opened only once per process
+    if (!memcmp(&g_ipc_open[i].h, &h, sizeof(h))) {
+      *ptr_out = (char*)g_ipc_open[i].base + offset;
+      return B2MM_OK;
+    }
+  if (g_ipc_n == 64) return fail(B2MM_ERR_UNSUPPORTED, "too many imported allocations");
+  void* base = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+  g_ipc_open[g_ipc_n].h = h;
+  g_ipc_open[g_ipc_n].base = base;
+  ++g_ipc_n;
+  *ptr_out = (char*)base + offset;
+  return B2MM_OK;
+}
+
+int b2mm_comm_barrier(void* comm, b2mm_stream_t stream) {
+  Comm* c = (Comm*)comm;
+  if (!c) return fail(B2MM_ERR_BAD_ARG, "null communicator");
+  ncclResult_t r = nccl().AllReduce(c->barrier_word, c->barrier_word, 1, ncclFloat32, ncclSum, c->nccl, (cudaStream_t)stream);
+  if (r != ncclSuccess) return nccl_fail("ncclAllReduce(barrier)", r);
+  return B2MM_OK;
+}
+
+int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void* const* peer_slabs, int rank, int world,
+                              int64_t M, int64_t n_local, int64_t K, int dtype, void* workspace,
+                              size_t workspace_bytes, b2mm_stream_t stream) {
+  const int es = dtype_bytes(dtype);
+  if (es == 0) return fail(B2MM_ERR_BAD_ARG, "unknown dtype %d", dtype);
+  if (!peer_slabs || world < 1 || world > 8 || rank < 0 || rank >= world)
+    return fail(B2MM_ERR_BAD_ARG, "bad rank/world (%d/%d; at most 8 destinations) or null slab list", rank, world);
+  // Destination d: slab `rank` of rank d's [world][M][n_local] buffer, as mapped into this process.
+  void* dst[8];
+  for (int d = 0; d < world; ++d) {
+    if (!peer_slabs[d]) return fail(B2MM_ERR_BAD_ARG, "null slab pointer for rank %d", d);
+    dst[d] = (char*)peer_slabs[d] + (size_t)rank * M * n_local * es;
+  }
+  return gemm_impl(A, B_local, nullptr, M, n_local, K, K, n_local, n_local, 1, 0, 0, 0, dtype, workspace, workspace_bytes,
+                   /*max_sms=*/0, (cudaStream_t)stream, dst, world);
 }
 
 int b2mm_gemm_allgather_overlap(void* comm, const void* A, const void* B_local, void* C_local, void* recv_slabs,

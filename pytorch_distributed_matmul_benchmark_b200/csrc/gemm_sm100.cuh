@@ -65,12 +65,21 @@ struct GemmParams {
   // 0: static round-robin over a grid of <= #SM CTAs.  1: the grid has one cluster per tile and
   // running clusters obtain further tiles from the hardware (cluster launch control).
   int dynamic;
+  int fanout;  // 0: store C through tmC; n > 0: store every chunk through fan.m[0..n)
   // Optional trace buffer (tools only; null in production): per CTA, per tile
   // iteration, the global-timer value at which the producer started the tile.
   unsigned long long* trace;
 };
 
 enum class InKind : int { BF16 = 0, FP16 = 1, TF32 = 2 };
+
+// Fan-out of the output: when GemmParams::fanout > 0 every finished chunk of C is stored to
+// fanout destinations (tensor maps over local and peer-GPU buffers, NVLink-mapped) instead of
+// to one — the all-gather of matrix_parallel done by the GEMM's own epilogue.
+constexpr int kMaxFanout = 8;
+struct FanoutMaps {
+  CUtensorMap m[kMaxFanout];
+};
 
 template <int kCtaGroup_, int BLOCK_N_, int kElemBytes_, int kSplit_, typename OutT_, bool kBKMajor_ = false,
           int kMBlocks_ = 1, int kChunkKB_ = 0>
@@ -193,7 +202,8 @@ template <class Cfg>
 __global__ void __launch_bounds__(Cfg::kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmA_lo,
-            const __grid_constant__ CUtensorMap tmB_lo, const GemmParams p) {
+            const __grid_constant__ CUtensorMap tmB_lo, const __grid_constant__ FanoutMaps fan,
+            const GemmParams p) {
   using namespace ptx;
   constexpr int G = Cfg::kCtaGroup;
   constexpr int kStages = Cfg::kStages;
@@ -463,6 +473,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t tempty_leader = (G == 2) ? mapa(tempty_bar, 0) : tempty_bar;
     uint32_t buf = 0;
 
+    // One 32-row x 128-byte chunk from staging to C — or to every destination of the fan-out.
+    auto store_chunk = [&](uint32_t sbuf, int col, int row, int b) {
+      if (p.fanout == 0) {
+        tma_store_3d(&tmC, sbuf, col, row, b);
+      } else {
+        for (int d = 0; d < p.fanout; ++d) tma_store_3d(&fan.m[d], sbuf, col, row, b);
+      }
+      tma_store_commit();
+    };
+
     // Move this warp's 32 rows of one accumulator (BLOCK_N columns at t_acc) to C, 128 bytes
     // per row at a time; hand the accumulator back (slot) as soon as it has been read.
     auto drain = [&](uint32_t t_acc, int row0, int col0, int b, int slot) {
@@ -511,8 +531,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          tma_store_3d(&tmC, sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
-          tma_store_commit();
+          store_chunk(sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
         }
         buf ^= 1u;
       }
@@ -570,8 +589,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_3d(&tmC, sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
-            tma_store_commit();
+            store_chunk(sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
           }
           buf ^= 1u;
         }

@@ -95,6 +95,8 @@ class Ops:
     all_gather_into: Callable  # (slabs, t) -> slabs           [dist.all_gather]
     matmul_allgather_overlap: Optional[Callable] = None  # (A, B_local, C_local, slabs, n_panels)
     bmm_allreduce_overlap: Optional[Callable] = None  # (A, B, C, n_panels)
+    shared_slabs: Optional[Callable] = None  # (M, n_local, dtype) -> SharedSlabs
+    matmul_allgather_fused: Optional[Callable] = None  # (A, B_local, shared) -> slabs
     synchronize: Callable = torch.cuda.synchronize
     event: Callable = lambda: torch.cuda.Event(enable_timing=True)
     destroy: Callable = lambda: None
@@ -115,6 +117,8 @@ def device_ops(rank: int, world_size: int, device: str) -> Ops:
         all_gather_into=comm.all_gather_into if comm else no_comm,
         matmul_allgather_overlap=comm.matmul_allgather_overlap if comm else None,
         bmm_allreduce_overlap=comm.bmm_allreduce_overlap if comm else None,
+        shared_slabs=comm.shared_slabs if comm else None,
+        matmul_allgather_fused=comm.matmul_allgather_fused if comm else None,
         destroy=comm.destroy if comm else (lambda: None),
     )
 

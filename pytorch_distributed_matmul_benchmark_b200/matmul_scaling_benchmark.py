@@ -9,6 +9,8 @@ Additive behaviour (flags the reference does not have):
                    (after backup/matmul_overlap_benchmark.py:93-180, without its races);
                    both the reference-style serial split and the end-to-end time are reported
   --panels P       row panels per GEMM in --overlap mode
+  --fused          matrix_parallel only: ONE kernel whose epilogue stores each C tile into every
+                   rank's gather buffer over NVLink (no collective kernel); reported like --overlap
   --batch-size B   total batch for batch_parallel (reference: 4, hard-coded at :283)
   --per-gpu-batch  fixed local batch per GPU (weak scaling; the reference's 4 // ws is 0 at ws=8)
 """
@@ -162,7 +164,7 @@ def benchmark_batch_parallel(matrix_size: int, batch_size: int, dtype: torch.dty
 def benchmark_matrix_parallel(matrix_size: int, dtype: torch.dtype, device: str, rank: int, world_size: int,
                               num_iterations: int = 50, warmup_iterations: int = 10,
                               ops: Optional[hostlib.Ops] = None, overlap: bool = False, panels: int = 4,
-                              check: bool = False) -> Tuple[float, float]:
+                              check: bool = False, fused: bool = False) -> Tuple[float, float]:
     """Mirror of matmul_scaling_benchmark.py:167-238: A replicated, B split by columns, C slabs gathered.
 
     The gathered result is ONE contiguous [world][N][N/world] buffer (the logical
@@ -216,6 +218,21 @@ def benchmark_matrix_parallel(matrix_size: int, dtype: torch.dtype, device: str,
             print(f"    Overlapped end-to-end: {avg_overlap*1000:.3f} ms ({panels} panels; serial sum {avg_total_time*1000:.3f} ms)")
         avg_total_time = avg_overlap
 
+    if fused and ops.matmul_allgather_fused is not None:
+        shared = ops.shared_slabs(matrix_size, end_col - start_col, dtype)
+        shared.local.zero_()
+        ops.synchronize()
+        dist.barrier()
+        for _ in range(min(warmup_iterations, 3)):
+            ops.matmul_allgather_fused(A, B_local, shared)
+        ops.synchronize()
+        dist.barrier()
+        avg_fused = _timed_loop(ops, lambda: ops.matmul_allgather_fused(A, B_local, shared), num_iterations)
+        if rank == 0:
+            print(f"    Fused GEMM+all_gather end-to-end: {avg_fused*1000:.3f} ms (one kernel + barrier; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
+        avg_total_time = avg_fused
+        slabs = shared.local
+
     if check and B_full is not None:
         ops.synchronize()
         C_global = torch.cat(list(slabs.unbind(0)), dim=1)  # [N][N]: slab r holds columns of rank r
@@ -237,7 +254,7 @@ def run_benchmarks(rank: int, world_size: int, matrix_sizes: List[int], dtype: t
                    num_iterations: int, warmup_iterations: int, ops: Optional[hostlib.Ops] = None,
                    device: Optional[str] = None, overlap: bool = False, panels: int = 4,
                    batch_size: int = hostlib.TOTAL_BATCH, per_gpu_batch: Optional[int] = None, check: bool = False,
-                   bench_fns: Optional[dict] = None, results: Optional[list] = None) -> None:
+                   bench_fns: Optional[dict] = None, results: Optional[list] = None, fused: bool = False) -> None:
     """Size loop, mode dispatch, aggregation and report of matmul_scaling_benchmark.py:251-347.
 
     `bench_fns` maps a ScalingMode to a stub `(size) -> (avg_s, tflops_per_gpu)`; tests use it to pin the report.
@@ -275,7 +292,8 @@ def run_benchmarks(rank: int, world_size: int, matrix_sizes: List[int], dtype: t
             else:
                 avg_time, tflops_per_gpu = benchmark_matrix_parallel(size, dtype, device, rank, world_size,
                                                                      num_iterations, warmup_iterations, ops=ops,
-                                                                     overlap=overlap, panels=panels, check=check)
+                                                                     overlap=overlap, panels=panels, check=check,
+                                                                     fused=fused)
 
             avg_time_all = hostlib.metric_all_reduce(avg_time, device, "avg")
             tflops_all = hostlib.metric_all_reduce(tflops_per_gpu, device,
@@ -303,7 +321,8 @@ def run_benchmarks(rank: int, world_size: int, matrix_sizes: List[int], dtype: t
                 if results is not None:
                     results.append({"size": size, "mode": mode.value, "n_gpus": world_size,
                                     "avg_time_ms": avg_time_all * 1000, "tflops_per_gpu": tflops_per_gpu,
-                                    "aggregate_tflops": tflops_all, "actual_tflops": actual, "overlap": overlap})
+                                    "aggregate_tflops": tflops_all, "actual_tflops": actual, "overlap": overlap,
+                                    "fused": fused})
         except torch.cuda.OutOfMemoryError:
             if rank == 0:
                 print(f"\n  ERROR: Out of memory for {size}x{size} matrices")
@@ -325,6 +344,8 @@ def build_parser() -> argparse.ArgumentParser:
                         choices=["independent", "batch_parallel", "matrix_parallel"],
                         help="Scaling mode (default: independent)")
     parser.add_argument("--overlap", action="store_true", help="Pipeline the collective behind compute (two streams)")
+    parser.add_argument("--fused", action="store_true",
+                        help="matrix_parallel: all_gather done by the GEMM epilogue over NVLink (one kernel)")
     parser.add_argument("--panels", type=int, default=4, help="Row panels per GEMM with --overlap (default: 4)")
     parser.add_argument("--batch-size", type=int, default=hostlib.TOTAL_BATCH,
                         help="Total batch for batch_parallel (default: 4, the reference's constant)")
@@ -352,7 +373,7 @@ def main(argv: Optional[List[str]] = None) -> None:
     try:
         run_benchmarks(rank, world_size, args.sizes, dtype, mode, args.iterations, args.warmup, ops=ops, device=device,
                        overlap=args.overlap, panels=args.panels, batch_size=args.batch_size,
-                       per_gpu_batch=args.per_gpu_batch, check=args.check, results=results)
+                       per_gpu_batch=args.per_gpu_batch, check=args.check, results=results, fused=args.fused)
     finally:
         ops.destroy()
         cleanup_distributed()

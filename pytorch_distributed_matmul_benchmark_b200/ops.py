@@ -127,6 +127,13 @@ def bmm(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None) ->
     return out
 
 
+class SharedSlabs:
+    """A rank's gather buffer plus the pointers under which every rank's buffer is visible here."""
+
+    def __init__(self, local: torch.Tensor, peer_ptrs, keepalive):
+        self.local, self.peer_ptrs, self._keepalive = local, peer_ptrs, keepalive
+
+
 class Communicator:
     """An ncclComm_t owned by libb2mm.so, bootstrapped over an existing torch process group.
 
@@ -181,6 +188,51 @@ class Communicator:
         slabs = torch.empty((self.world_size,) + tuple(t.shape), dtype=t.dtype, device=t.device)
         self.all_gather_into(slabs, t)
         return list(slabs.unbind(0))
+
+    def barrier(self) -> None:
+        """Cross-rank barrier on the current stream (dist.barrier() for enqueued work)."""
+        _lib.check(_lib.load().b2mm_comm_barrier(self._comm, _stream_ptr()))
+
+    def shared_slabs(self, M: int, n_local: int, dtype: torch.dtype) -> "SharedSlabs":
+        """A [world][M][n_local] gather buffer on every rank, each mapped into every other rank (CUDA IPC).
+
+        torch allocates (device memory is torch's business); the handles travel through the existing
+        process group; the library only ever sees the resulting raw pointers.
+        """
+        import torch.distributed as dist
+        local = torch.empty((self.world_size, M, n_local), dtype=dtype, device=self.device)
+        lib = _lib.load()
+        handle = (ctypes.c_ubyte * 64)()
+        offset = ctypes.c_int64()
+        _lib.check(lib.b2mm_ipc_export(local.data_ptr(), ctypes.cast(handle, ctypes.c_void_p), ctypes.byref(offset)))
+        gathered = [None] * self.world_size
+        dist.all_gather_object(gathered, (bytes(handle), offset.value))
+        ptrs, keep = [], [local]
+        with torch.cuda.device(self.device):
+            for r, (h, off) in enumerate(gathered):
+                if r == self.rank:
+                    ptrs.append(local.data_ptr())
+                else:
+                    p = ctypes.c_void_p()
+                    buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+                    _lib.check(lib.b2mm_ipc_import(ctypes.cast(buf, ctypes.c_void_p), off, ctypes.byref(p)))
+                    ptrs.append(p.value)
+        return SharedSlabs(local, (ctypes.c_void_p * self.world_size)(*ptrs), keep)
+
+    def matmul_allgather_fused(self, A: torch.Tensor, B_local: torch.Tensor, shared: "SharedSlabs") -> torch.Tensor:
+        """C_local = A @ B_local with the all_gather done by the GEMM epilogue (peer TMA stores), then a barrier."""
+        _require_cuda(A, B_local)
+        M, K = A.shape
+        n_local = B_local.shape[1]
+        if tuple(shared.local.shape) != (self.world_size, M, n_local) or shared.local.dtype != A.dtype:
+            raise RuntimeError("shared slabs do not match the problem")
+        code = _dtype_code(A)
+        ws, ws_bytes = workspace_for(M, n_local, K, 1, code, A.device)
+        _lib.check(_lib.load().b2mm_gemm_allgather_fused(
+            A.data_ptr(), B_local.data_ptr(), shared.peer_ptrs, self.rank, self.world_size, M, n_local, K, code,
+            ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr()))
+        self.barrier()
+        return shared.local
 
     def matmul_allgather_overlap(self, A: torch.Tensor, B_local: torch.Tensor, C_local: torch.Tensor,
                                  slabs: torch.Tensor, n_panels: int = 4) -> torch.Tensor:

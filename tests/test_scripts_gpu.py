@@ -47,7 +47,8 @@ def test_scaling_script_single_gpu_all_modes(dtype):
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
 @pytest.mark.parametrize("mode,extra", [("independent", []), ("batch_parallel", []), ("matrix_parallel", []),
                                         ("batch_parallel", ["--overlap", "--panels", "2"]),
-                                        ("matrix_parallel", ["--overlap", "--panels", "4"])])
+                                        ("matrix_parallel", ["--overlap", "--panels", "4"]),
+                                        ("matrix_parallel", ["--fused"])])
 def test_scaling_script_two_gpus(mode, extra):
     out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                 "--master-addr=127.0.0.1", f"--master-port={_free_port()}", "matmul_scaling_benchmark.py", "--sizes",
@@ -55,5 +56,7 @@ def test_scaling_script_two_gpus(mode, extra):
     assert "Collective operations verified successfully across 2 GPUs" in out
     assert "Results for 2048x2048:" in out and "ERROR" not in out and "FAIL" not in out
     assert "-> OK" in out
-    if extra:
+    if "--overlap" in extra:
         assert "Overlapped end-to-end:" in out
+    if "--fused" in extra:
+        assert "Fused GEMM+all_gather end-to-end:" in out

@@ -106,6 +106,7 @@ struct Operands {
   int dtype;
   void* const* fan_ptrs;  // fanout destinations for C (null: just C)
   int fanout;
+  int tiles_per_cluster;
 };
 
 template <class Cfg>
@@ -157,6 +158,7 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   p.hint_b = kHints[env_int("B2MM_HINT_B", 0) % 3];
   p.trace = g_trace;
   p.fanout = o.fanout;
+  p.max_tiles = o.tiles_per_cluster;
   // Dynamic (hardware work-stealing) scheduling unless the caller capped the SMs.
   const char* sched = getenv("B2MM_SCHED");
   p.dynamic = (max_sms > 0 || (sched && !strcmp(sched, "static"))) ? 0 : 1;
@@ -215,8 +217,11 @@ size_t gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int 
 
 int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
               int64_t ldc, int64_t batch, int64_t sA, int64_t sB, int64_t sC, int dtype, void* workspace,
-              size_t workspace_bytes, int max_sms, cudaStream_t stream, void* const* fan_ptrs, int fanout) {
+              size_t workspace_bytes, cudaStream_t stream, const GemmOpts& opts) {
   const int es = dtype_bytes(dtype);
+  const int max_sms = opts.max_sms;
+  void* const* fan_ptrs = opts.fan_ptrs;
+  const int fanout = opts.fanout;
   if (fanout < 0 || fanout > kMaxFanout) return fail(B2MM_ERR_UNSUPPORTED, "fan-out of %d destinations (max %d)", fanout, kMaxFanout);
   if (fanout > 0) {
     if (!fan_ptrs) return fail(B2MM_ERR_BAD_ARG, "null destination list");
@@ -239,7 +244,8 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
   if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX || batch > 65535)
     return fail(B2MM_ERR_UNSUPPORTED, "dimension too large");
 
-  Operands o{A, B, nullptr, nullptr, C, M, N, K, lda, ldb, ldc, batch, sA, sB, sC, dtype, fan_ptrs, fanout};
+  Operands o{A, B, nullptr, nullptr, C, M, N, K, lda, ldb, ldc, batch, sA, sB, sC, dtype, fan_ptrs, fanout,
+             opts.tiles_per_cluster};
   const int sms = device_sm_count();
   int clusters = (max_sms > 0 && max_sms < sms ? max_sms : sms) / 2;
   if (clusters < 1) clusters = 1;
@@ -282,6 +288,9 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
   if (m_blocks != 1 && m_blocks != 2) {
     const int64_t tall_tiles = ((M + 511) / 512) * ((N + 255) / 256) * batch;
     m_blocks = (tall_tiles >= clusters) ? 2 : 1;
+    // With remote destinations the epilogue drains at NVLink speed: keep TMEM double buffered so
+    // the next tile's main loop runs meanwhile.
+    if (fanout > 1) m_blocks = 1;
   }
 
   if (dtype == B2MM_BF16) {
@@ -343,7 +352,7 @@ int b2mm_gemm(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
               int64_t ldc, int64_t batch, int64_t strideA, int64_t strideB, int64_t strideC, int dtype,
               void* workspace, size_t workspace_bytes, b2mm_stream_t stream) {
   return b2mm::gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, batch, strideA, strideB, strideC, dtype, workspace,
-                         workspace_bytes, /*max_sms=*/0, (cudaStream_t)stream);
+                         workspace_bytes, (cudaStream_t)stream);
 }
 
 int b2mm_gemm_fp32_noalloc(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t K, int64_t lda,
@@ -360,7 +369,7 @@ int b2mm_gemm_fp32_noalloc(const float* A, const float* B, float* C, int64_t M, 
   if (int rc = noalloc_scratch_address(&scratch)) return rc;
   // Same kernels as b2mm_gemm(dtype = fp32); the split pre-pass rewrites every scratch byte the GEMM reads.
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 1, 0, 0, 0, B2MM_FP32, scratch, (size_t)B2MM_NOALLOC_SCRATCH_BYTES,
-                   /*max_sms=*/0, (cudaStream_t)stream, nullptr, 0);
+                   (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -81,10 +81,23 @@ static bool nccl_type(int dtype, ncclDataType_t* t) {
   }
 }
 
-static int comm_sms() {
+// How the panel GEMMs of the stream-pipelined drivers make room for the collective kernels.
+// Default: dynamic scheduler whose clusters retire every B2MM_TILES_PER_CLUSTER tiles (2), so that the
+// pending blocks of the higher-priority comm stream get SMs within a tile or two and give them back
+// when done.  B2MM_COMM_SMS=n > 0 selects the older scheme instead: static scheduler on (#SM - n) SMs.
+static GemmOpts overlap_opts() {
+  GemmOpts o;
   const char* v = getenv("B2MM_COMM_SMS");
-  int n = (v && *v) ? atoi(v) : 16;
-  return n < 0 ? 0 : n;
+  const int reserve = (v && *v) ? atoi(v) : 0;
+  if (reserve > 0) {
+    const int sms = device_sm_count();
+    o.max_sms = sms - reserve > 2 ? sms - reserve : sms;
+  } else {
+    const char* t = getenv("B2MM_TILES_PER_CLUSTER");
+    o.tiles_per_cluster = (t && *t) ? atoi(t) : 2;
+    if (o.tiles_per_cluster < 0) o.tiles_per_cluster = 0;
+  }
+  return o;
 }
 
 }  // namespace b2mm
@@ -248,8 +261,11 @@ int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void* const* p
     if (!peer_slabs[d]) return fail(B2MM_ERR_BAD_ARG, "null slab pointer for rank %d", d);
     dst[d] = (char*)peer_slabs[d] + (size_t)rank * M * n_local * es;
   }
+  GemmOpts opts;
+  opts.fan_ptrs = dst;
+  opts.fanout = world;
   return gemm_impl(A, B_local, nullptr, M, n_local, K, K, n_local, n_local, 1, 0, 0, 0, dtype, workspace, workspace_bytes,
-                   /*max_sms=*/0, (cudaStream_t)stream, dst, world);
+                   (cudaStream_t)stream, opts);
 }
 
 int b2mm_gemm_allgather_overlap(void* comm, const void* A, const void* B_local, void* C_local, void* recv_slabs,
@@ -264,13 +280,12 @@ int b2mm_gemm_allgather_overlap(void* comm, const void* A, const void* B_local, 
   const int es = dtype_bytes(dtype);
   const int64_t mp = M / n_panels;
   const int64_t slab = M * n_local;  // elements per rank in recv_slabs
-  const int sms = device_sm_count();
-  const int gemm_sms = sms - comm_sms() > 2 ? sms - comm_sms() : sms;
+  const GemmOpts opts = overlap_opts();
   for (int i = 0; i < n_panels; ++i) {
     const char* a = (const char*)A + (size_t)i * mp * K * es;
     char* cl = (char*)C_local + (size_t)i * mp * n_local * es;
     int rc = gemm_impl(a, B_local, cl, mp, n_local, K, K, n_local, n_local, 1, 0, 0, 0, dtype, workspace,
-                       workspace_bytes, gemm_sms, compute);
+                       workspace_bytes, compute, opts);
     if (rc) return rc;
     if (cudaEventRecord(c->panel_done[i], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
     if (cudaStreamWaitEvent(cs, c->panel_done[i], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
@@ -303,15 +318,14 @@ int b2mm_gemm_allreduce_overlap(void* comm, const void* A, const void* B, void* 
   cudaStream_t compute = (cudaStream_t)compute_, cs = (cudaStream_t)comm_stream_;
   const int es = dtype_bytes(dtype);
   const int64_t mp = N / n_panels;
-  const int sms = device_sm_count();
-  const int gemm_sms = sms - comm_sms() > 2 ? sms - comm_sms() : sms;
+  const GemmOpts opts = overlap_opts();
   int ev = 0;
   for (int64_t b = 0; b < local_batch; ++b) {
     for (int i = 0; i < n_panels; ++i, ++ev) {
       const char* a = (const char*)A + ((size_t)b * N * N + (size_t)i * mp * N) * es;
       const char* bb = (const char*)B + (size_t)b * N * N * es;
       char* cc = (char*)C + ((size_t)b * N * N + (size_t)i * mp * N) * es;
-      int rc = gemm_impl(a, bb, cc, mp, N, N, N, N, N, 1, 0, 0, 0, dtype, workspace, workspace_bytes, gemm_sms, compute);
+      int rc = gemm_impl(a, bb, cc, mp, N, N, N, N, N, 1, 0, 0, 0, dtype, workspace, workspace_bytes, compute, opts);
       if (rc) return rc;
       if (cudaEventRecord(c->panel_done[ev], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
       if (cudaStreamWaitEvent(cs, c->panel_done[ev], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");

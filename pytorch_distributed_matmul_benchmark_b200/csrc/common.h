@@ -14,12 +14,16 @@ int device_sm_count();
 
 size_t gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype);
 
-// b2mm_gemm with a cap on the SMs the persistent grid may occupy (0 = all; the overlap drivers
-// leave SMs free for the concurrently running collective) and an optional fan-out of C: when
-// fanout > 0 the result is stored to fan_ptrs[0..fanout) (local or peer-mapped) and `C` is ignored.
+// Options of the internal GEMM entry beyond what b2mm_gemm exposes.
+struct GemmOpts {
+  int max_sms = 0;                    // > 0: static scheduler on at most this many SMs
+  void* const* fan_ptrs = nullptr;    // fanout > 0: C is stored to fan_ptrs[0..fanout) (local or peer-mapped)
+  int fanout = 0;
+  int tiles_per_cluster = 0;          // dynamic scheduler: clusters retire after this many tiles (0 = never)
+};
+
 int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
               int64_t ldc, int64_t batch, int64_t sA, int64_t sB, int64_t sC, int dtype, void* workspace,
-              size_t workspace_bytes, int max_sms, cudaStream_t stream, void* const* fan_ptrs = nullptr,
-              int fanout = 0);
+              size_t workspace_bytes, cudaStream_t stream, const GemmOpts& opts = GemmOpts());
 
 }  // namespace b2mm

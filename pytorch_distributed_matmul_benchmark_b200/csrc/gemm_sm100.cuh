@@ -66,6 +66,10 @@ struct GemmParams {
   // running clusters obtain further tiles from the hardware (cluster launch control).
   int dynamic;
   int fanout;  // 0: store C through tmC; n > 0: store every chunk through fan.m[0..n)
+  // Dynamic mode only: a cluster retires after this many tiles (0 = runs until no tile is left).
+  // Retiring frees its two SMs, which lets pending blocks of a higher-priority stream (the
+  // collective of the previous panel) in; the grid's remaining clusters are launched as usual.
+  int max_tiles;
   // Optional trace buffer (tools only; null in production): per CTA, per tile
   // iteration, the global-timer value at which the producer started the tile.
   unsigned long long* trace;
@@ -275,6 +279,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int tile;
     int slot;
     uint32_t phase;
+    int done = 0;  // tiles already taken by this walker
   };
   const uint32_t clc_empty_leader = (G == 2) ? mapa(clc_empty, 0) : clc_empty;
   // kWarp: called by all 32 lanes of a warp (one lane releases the slot); else by a single thread.
@@ -283,6 +288,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       q.tile += num_clusters;
       return q.tile < p.num_tiles;
     }
+    if (p.max_tiles > 0 && ++q.done >= p.max_tiles) return false;  // every walker counts the same sequence
     mbar_wait(clc_full + 8u * q.slot, q.phase);
     uint32_t ctaid_x;
     const bool ok = clc_query(clc_resp + 16u * q.slot, ctaid_x);
@@ -456,6 +462,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (p.dynamic && cta_rank == 0 && elect_one()) {
       TileSeq q{0, 0, 0u};
       for (;;) {
+        if (p.max_tiles > 0 && q.done + 1 >= p.max_tiles) break;  // the cluster retires after this tile
         mbar_wait<true>(clc_empty + 8u * q.slot, q.phase ^ 1u);
         for (uint32_t c = 0; c < (uint32_t)G; ++c)
           mbar_arrive_expect_tx_cluster(G == 2 ? mapa(clc_full + 8u * q.slot, c) : clc_full + 8u * q.slot, 16u);

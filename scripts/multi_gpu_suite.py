@@ -69,14 +69,28 @@ t_ar = timed(lambda: comm.all_reduce(C3))
 bytes_ar = C3.numel() * 2
 bp = {"compute_ms": t_gemm, "comm_ms": t_ar, "serial_ms": t_gemm + t_ar, "serial_eff": t1 / (t_gemm + t_ar),
       "allreduce_busbw_GBs": bytes_ar * 2 * (ws - 1) / ws / (t_ar * 1e-3) / 1e9, "overlap": []}
-for sms in (8, 16, 32):
-    for panels in (4, 8):
-        os.environ["B2MM_COMM_SMS"] = str(sms)
-        t = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, panels))
-        bp["overlap"].append({"comm_sms": sms, "panels": panels, "ms": t, "eff": t1 / t})
-bp["best"] = min(bp["overlap"], key=lambda r: r["ms"])
+configs = [("retire", t, p_) for t in (1, 2, 4) for p_ in (4, 8)] + [("reserve", 16, 8)]
+for kind, val, panels in configs:
+    os.environ.pop("B2MM_COMM_SMS", None)
+    os.environ.pop("B2MM_TILES_PER_CLUSTER", None)
+    os.environ["B2MM_COMM_SMS" if kind == "reserve" else "B2MM_TILES_PER_CLUSTER"] = str(val)
+    t = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, panels))
+    bp["overlap"].append({"scheme": kind, "value": val, "panels": panels, "ms": t, "eff_vs_cold_T1": t1 / t})
+best = min(bp["overlap"], key=lambda r: r["ms"])
+os.environ.pop("B2MM_COMM_SMS", None)
+os.environ.pop("B2MM_TILES_PER_CLUSTER", None)
+os.environ["B2MM_COMM_SMS" if best["scheme"] == "reserve" else "B2MM_TILES_PER_CLUSTER"] = str(best["value"])
+# weak-scaling efficiency measured fairly: the 1-GPU time (GEMM alone, no comm) and the N-GPU time
+# (GEMM + pipelined all_reduce) interleaved in the same thermal state, three rounds
+rounds = []
+for _ in range(3):
+    tg = timed(lambda: b2.bmm(A3, B3, out=C3), iters=8, warm=1)
+    to = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, best["panels"]), iters=8, warm=1)
+    rounds.append({"gemm_only_ms": tg, "overlap_ms": to, "weak_eff": tg / to})
+bp["best"] = best
+bp["interleaved_rounds"] = rounds
+bp["weak_scaling_eff"] = sum(r["weak_eff"] for r in rounds) / len(rounds)
 res["batch_parallel_weak_b1"] = bp
-os.environ["B2MM_COMM_SMS"] = str(bp["best"]["comm_sms"])
 
 # ---- matrix_parallel ----
 if N % ws == 0:
@@ -98,6 +112,9 @@ if N % ws == 0:
     dist.barrier()
     mp["fused_ms"] = timed(lambda: comm.matmul_allgather_fused(A, B_local, shared))
     mp["fused_actual_tflops"] = flop / mp["fused_ms"] / 1e9
+    os.environ["B2MM_M_BLOCKS"] = "2"  # tall single-buffered tiles, for comparison (default in fused mode: 1)
+    mp["fused_tall_tiles_ms"] = timed(lambda: comm.matmul_allgather_fused(A, B_local, shared))
+    os.environ.pop("B2MM_M_BLOCKS")
     t_bar = timed(lambda: comm.barrier(), iters=50)
     mp["barrier_ms"] = t_bar
     torch.cuda.synchronize()

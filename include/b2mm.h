@@ -202,6 +202,27 @@ B2MM_API int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void*
                                        b2mm_stream_t stream);
 
 /*
+ * In-place SUM over ranks of `count` elements, done by this library's own kernel over peer-mapped
+ * buffers instead of NCCL (replaces dist.all_reduce(C, op=SUM), matmul_scaling_benchmark.py:125,150):
+ * each rank pulls its 1/world slice from every rank over NVLink, adds in fp32, rounds once, and pushes
+ * the result into every rank's buffer.  peer_bufs[r] = rank r's buffer as mapped here (b2mm_ipc_import;
+ * own rank: the local pointer).  Includes the cross-rank barriers before and after.  world <= 8.
+ */
+B2MM_API int b2mm_all_reduce_p2p(void* comm, void* const* peer_bufs, int64_t count, int dtype, b2mm_stream_t stream);
+
+/*
+ * batch_parallel as a pipeline of this library's own kernels (matmul_scaling_benchmark.py:142 + :150):
+ * C = bmm(A, B) in row panels on `compute`, written into peer_C[rank]; behind each panel, on
+ * `comm_stream`: barrier, then the peer-memory all-reduce of that panel (as b2mm_all_reduce_p2p).
+ * The panel GEMMs use the dynamic scheduler with retiring clusters so that the small reduce kernels
+ * find SMs.  On return `compute` waits for the last reduction.  A, B, C: (local_batch, N, N).
+ */
+B2MM_API int b2mm_gemm_allreduce_p2p(void* comm, const void* A, const void* B, void* const* peer_C,
+                                     int64_t N, int64_t local_batch, int dtype, int n_panels,
+                                     void* workspace, size_t workspace_bytes,
+                                     b2mm_stream_t compute, b2mm_stream_t comm_stream);
+
+/*
  * matrix_parallel with the gather pipelined behind compute
  * (after backup/matmul_overlap_benchmark.py:93-180, made race-free):
  * C_local = A * B_local is computed in `n_panels` row panels on `compute`;

@@ -1,0 +1,117 @@
+// All-reduce (SUM) over peer-mapped buffers, one launch per rank: every rank owns 1/world of the
+// range; it PULLS its slice from every rank over NVLink, adds the `world` values in fp32 (one
+// rounding to the storage type at the end — tighter than a chain of 16-bit adds), and PUSHES the
+// result into every rank's buffer.  In place: a slice is read only by its owner, so nothing is
+// overwritten before it has been read.
+//
+// HBM / NVLink bound: per element each rank reads `world` values (world-1 remote) and writes `world`
+// (world-1 remote); 2 * (world-1)/world * bytes cross each direction of the link, the same as a
+// ring.  The grid is small on purpose (it runs beside the GEMM of the next panel).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace b2mm {
+
+struct PeerPtrs {
+  void* p[8];
+};
+
+template <typename T>
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]);
+template <>
+__device__ __forceinline__ void unpack8<__nv_bfloat16>(const uint4& v, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+template <>
+__device__ __forceinline__ void unpack8<__half>(const uint4& v, float (&f)[8]) {
+  const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __half22float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+template <typename T>
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]);
+template <>
+__device__ __forceinline__ uint4 pack8<__nv_bfloat16>(const float (&f)[8]) {
+  uint4 v;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return v;
+}
+template <>
+__device__ __forceinline__ uint4 pack8<__half>(const float (&f)[8]) {
+  uint4 v;
+  __half2* h = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+  return v;
+}
+
+// `vec_begin`/`vec_count`: this launch's range in 16-byte vectors (already restricted to the slice
+// this rank owns).  kUnroll independent vectors per thread keep enough loads in flight for NVLink.
+template <typename T, int kUnroll>
+__global__ void __launch_bounds__(512) allreduce_p2p_kernel(PeerPtrs ptrs, int world, int64_t vec_begin, int64_t vec_count) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < vec_count; base += stride * kUnroll) {
+    float acc[kUnroll][sizeof(T) == 4 ? 4 : 8];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+      for (int j = 0; j < (sizeof(T) == 4 ? 4 : 8); ++j) acc[u][j] = 0.f;
+    for (int r = 0; r < world; ++r) {
+      const uint4* src = reinterpret_cast<const uint4*>(ptrs.p[r]) + vec_begin;
+      uint4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + u * stride;
+        if (i < vec_count) asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i));
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (base + u * stride < vec_count) {
+          if constexpr (sizeof(T) == 4) {
+            acc[u][0] += __uint_as_float(v[u].x);
+            acc[u][1] += __uint_as_float(v[u].y);
+            acc[u][2] += __uint_as_float(v[u].z);
+            acc[u][3] += __uint_as_float(v[u].w);
+          } else {
+            float f[8];
+            unpack8<T>(v[u], f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[u][j] += f[j];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + u * stride;
+      if (i < vec_count) {
+        uint4 out;
+        if constexpr (sizeof(T) == 4) {
+          out = make_uint4(__float_as_uint(acc[u][0]), __float_as_uint(acc[u][1]), __float_as_uint(acc[u][2]), __float_as_uint(acc[u][3]));
+        } else {
+          out = pack8<T>(acc[u]);
+        }
+        for (int d = 0; d < world; ++d) {
+          uint4* dst = reinterpret_cast<uint4*>(ptrs.p[d]) + vec_begin + i;
+          asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(out.x), "r"(out.y), "r"(out.z), "r"(out.w) : "memory");
+        }
+      }
+    }
+  }
+}
+
+}  // namespace b2mm

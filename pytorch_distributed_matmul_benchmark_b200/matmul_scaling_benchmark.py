@@ -9,8 +9,10 @@ Additive behaviour (flags the reference does not have):
                    (after backup/matmul_overlap_benchmark.py:93-180, without its races);
                    both the reference-style serial split and the end-to-end time are reported
   --panels P       row panels per GEMM in --overlap mode
-  --fused          matrix_parallel only: ONE kernel whose epilogue stores each C tile into every
-                   rank's gather buffer over NVLink (no collective kernel); reported like --overlap
+  --fused          matrix_parallel: ONE kernel whose epilogue stores each C tile into every rank's gather
+                   buffer over NVLink (no collective kernel).  batch_parallel: row-panel pipeline of the
+                   library's own kernels — GEMM panels, then a peer-memory all-reduce (pull, fp32 add,
+                   push) behind each panel.  Reported like --overlap
   --batch-size B   total batch for batch_parallel (reference: 4, hard-coded at :283)
   --per-gpu-batch  fixed local batch per GPU (weak scaling; the reference's 4 // ws is 0 at ws=8)
 """
@@ -113,7 +115,8 @@ def benchmark_independent(matrix_size: int, dtype: torch.dtype, device: str, ran
 def benchmark_batch_parallel(matrix_size: int, batch_size: int, dtype: torch.dtype, device: str, rank: int,
                              world_size: int, num_iterations: int = 50, warmup_iterations: int = 10,
                              ops: Optional[hostlib.Ops] = None, overlap: bool = False, panels: int = 4,
-                             local_batch_size: Optional[int] = None, check: bool = False) -> Tuple[float, float]:
+                             local_batch_size: Optional[int] = None, check: bool = False,
+                             fused: bool = False) -> Tuple[float, float]:
     """Mirror of matmul_scaling_benchmark.py:106-165: bmm on the local batch, then all_reduce(C, SUM)."""
     if local_batch_size is None:
         local_batch_size = batch_size // world_size  # :111 (0 at ws=8 with the default total of 4)
@@ -156,6 +159,25 @@ def benchmark_batch_parallel(matrix_size: int, batch_size: int, dtype: torch.dty
         if rank == 0:
             print(f"    Overlapped end-to-end: {avg_overlap*1000:.3f} ms ({panels} panels; serial sum {avg_total_time*1000:.3f} ms)")
         avg_total_time = avg_overlap
+
+    if fused and comm_on and local_batch_size > 0 and ops.bmm_allreduce_p2p is not None:
+        shared = ops.shared_like(C)
+        for _ in range(min(warmup_iterations, 3)):
+            ops.bmm_allreduce_p2p(A, B, shared, panels)
+        ops.synchronize()
+        dist.barrier()
+        avg_fused = _timed_loop(ops, lambda: ops.bmm_allreduce_p2p(A, B, shared, panels), num_iterations)
+        if rank == 0:
+            print(f"    Fused GEMM+all_reduce (peer memory) end-to-end: {avg_fused*1000:.3f} ms ({panels} panels; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
+        if check:  # against the NCCL all_reduce of the same product: two roundings of one sum, at most ~1 ulp apart
+            ops.bmm(A, B, out=C)
+            ops.all_reduce(C)
+            ops.synchronize()
+            ref = C.double()
+            rms = ref.pow(2).mean().sqrt()
+            err = ((shared.local.double() - ref).abs() / (ref.abs() + rms)).max().item()
+            _report_check(rank, err / 2 / max(world_size // 2, 1), dtype)
+        avg_total_time = avg_fused
 
     tflops_per_gpu = calculate_tflops(matrix_size, avg_total_time, num_ops=local_batch_size) if avg_total_time > 0 else 0.0
     return avg_total_time, tflops_per_gpu
@@ -288,7 +310,7 @@ def run_benchmarks(rank: int, world_size: int, matrix_sizes: List[int], dtype: t
             elif mode == ScalingMode.BATCH_PARALLEL:
                 avg_time, tflops_per_gpu = benchmark_batch_parallel(
                     size, total_batch, dtype, device, rank, world_size, num_iterations, warmup_iterations, ops=ops,
-                    overlap=overlap, panels=panels, local_batch_size=per_gpu_batch, check=check)
+                    overlap=overlap, panels=panels, local_batch_size=per_gpu_batch, check=check, fused=fused)
             else:
                 avg_time, tflops_per_gpu = benchmark_matrix_parallel(size, dtype, device, rank, world_size,
                                                                      num_iterations, warmup_iterations, ops=ops,

@@ -193,21 +193,20 @@ class Communicator:
         """Cross-rank barrier on the current stream (dist.barrier() for enqueued work)."""
         _lib.check(_lib.load().b2mm_comm_barrier(self._comm, _stream_ptr()))
 
-    def shared_slabs(self, M: int, n_local: int, dtype: torch.dtype) -> "SharedSlabs":
-        """A [world][M][n_local] gather buffer on every rank, each mapped into every other rank (CUDA IPC).
+    def share(self, local: torch.Tensor) -> "SharedSlabs":
+        """Map every rank's `local` (same shape on all ranks) into every other rank (CUDA IPC over NVLink).
 
-        torch allocates (device memory is torch's business); the handles travel through the existing
-        process group; the library only ever sees the resulting raw pointers.
+        torch allocates (device memory is torch's business); the 64-byte handles travel through the
+        existing process group; the library only ever sees the resulting raw pointers.
         """
         import torch.distributed as dist
-        local = torch.empty((self.world_size, M, n_local), dtype=dtype, device=self.device)
         lib = _lib.load()
         handle = (ctypes.c_ubyte * 64)()
         offset = ctypes.c_int64()
         _lib.check(lib.b2mm_ipc_export(local.data_ptr(), ctypes.cast(handle, ctypes.c_void_p), ctypes.byref(offset)))
         gathered = [None] * self.world_size
         dist.all_gather_object(gathered, (bytes(handle), offset.value))
-        ptrs, keep = [], [local]
+        ptrs = []
         with torch.cuda.device(self.device):
             for r, (h, off) in enumerate(gathered):
                 if r == self.rank:
@@ -217,7 +216,33 @@ class Communicator:
                     buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
                     _lib.check(lib.b2mm_ipc_import(ctypes.cast(buf, ctypes.c_void_p), off, ctypes.byref(p)))
                     ptrs.append(p.value)
-        return SharedSlabs(local, (ctypes.c_void_p * self.world_size)(*ptrs), keep)
+        return SharedSlabs(local, (ctypes.c_void_p * self.world_size)(*ptrs), [local])
+
+    def shared_slabs(self, M: int, n_local: int, dtype: torch.dtype) -> "SharedSlabs":
+        """A [world][M][n_local] gather buffer on every rank, each visible to every other rank."""
+        return self.share(torch.empty((self.world_size, M, n_local), dtype=dtype, device=self.device))
+
+    def shared_like(self, t: torch.Tensor) -> "SharedSlabs":
+        """A buffer shaped like `t` on every rank, each visible to every other rank (for the p2p all_reduce)."""
+        return self.share(torch.empty_like(t))
+
+    def all_reduce_p2p(self, shared: "SharedSlabs") -> torch.Tensor:
+        """In-place SUM of shared.local over ranks by the library's own NVLink kernel (fp32 adds, one rounding)."""
+        t = shared.local
+        _lib.check(_lib.load().b2mm_all_reduce_p2p(self._comm, shared.peer_ptrs, t.numel(), _dtype_code(t), _stream_ptr()))
+        return t
+
+    def bmm_allreduce_p2p(self, A: torch.Tensor, B: torch.Tensor, shared_C: "SharedSlabs", n_panels: int = 4) -> torch.Tensor:
+        """C = bmm(A, B) into shared_C.local in row panels, each panel summed over ranks by the p2p kernel behind it."""
+        _require_cuda(A, B)
+        b, N, _ = A.shape
+        code = _dtype_code(A)
+        ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)
+        self.comm_stream.wait_stream(torch.cuda.current_stream())
+        _lib.check(_lib.load().b2mm_gemm_allreduce_p2p(
+            self._comm, A.data_ptr(), B.data_ptr(), shared_C.peer_ptrs, N, b, code, n_panels,
+            ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(), self.comm_stream.cuda_stream))
+        return shared_C.local
 
     def matmul_allgather_fused(self, A: torch.Tensor, B_local: torch.Tensor, shared: "SharedSlabs") -> torch.Tensor:
         """C_local = A @ B_local with the all_gather done by the GEMM epilogue (peer TMA stores), then a barrier."""

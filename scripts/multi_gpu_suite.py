@@ -51,6 +51,19 @@ def timed(fn, iters=ITERS, warm=WARM):
     return max_ranks(s.elapsed_time(e) / iters)
 
 
+def timed_each(fn, iters=12):
+    """Per-iteration device times (ms) on this rank, no warm-up: shows ramp effects."""
+    torch.cuda.synchronize()
+    dist.barrier()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+    ev[0].record()
+    for i in range(iters):
+        fn()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    return [round(ev[i].elapsed_time(ev[i + 1]), 3) for i in range(iters)]
+
+
 res = {"size": N, "world": ws, "dtype": "bfloat16", "iters": ITERS}
 flop = 2.0 * N ** 3
 
@@ -69,7 +82,7 @@ t_ar = timed(lambda: comm.all_reduce(C3))
 bytes_ar = C3.numel() * 2
 bp = {"compute_ms": t_gemm, "comm_ms": t_ar, "serial_ms": t_gemm + t_ar, "serial_eff": t1 / (t_gemm + t_ar),
       "allreduce_busbw_GBs": bytes_ar * 2 * (ws - 1) / ws / (t_ar * 1e-3) / 1e9, "overlap": []}
-configs = [("retire", t, p_) for t in (1, 2, 4) for p_ in (4, 8)] + [("reserve", 16, 8)]
+configs = [("retire", 1, 4), ("retire", 1, 8), ("retire", 2, 8), ("reserve", 16, 8), ("reserve", 8, 8)]
 for kind, val, panels in configs:
     os.environ.pop("B2MM_COMM_SMS", None)
     os.environ.pop("B2MM_TILES_PER_CLUSTER", None)
@@ -87,6 +100,36 @@ for _ in range(3):
     tg = timed(lambda: b2.bmm(A3, B3, out=C3), iters=8, warm=1)
     to = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, best["panels"]), iters=8, warm=1)
     rounds.append({"gemm_only_ms": tg, "overlap_ms": to, "weak_eff": tg / to})
+# the library's own pipeline: GEMM panels + peer-memory all-reduce behind each panel
+sharedC = comm.shared_like(C3)
+t_p2p_alone = timed(lambda: comm.all_reduce_p2p(sharedC))
+bp["p2p_allreduce_alone_ms"] = t_p2p_alone
+bp["p2p_allreduce_busbw_GBs"] = bytes_ar * 2 * (ws - 1) / ws / (t_p2p_alone * 1e-3) / 1e9
+bp["p2p"] = []
+for tiles in (1,):
+    for panels in (4,):
+        os.environ["B2MM_TILES_PER_CLUSTER"] = str(tiles)
+        t = timed(lambda: comm.bmm_allreduce_p2p(A3, B3, sharedC, panels))
+        bp["p2p"].append({"tiles_per_cluster": tiles, "panels": panels, "ms": t})
+bestp = min(bp["p2p"], key=lambda r: r["ms"])
+os.environ["B2MM_TILES_PER_CLUSTER"] = str(bestp["tiles_per_cluster"])
+prounds = []
+for _ in range(1):
+    tg = timed(lambda: b2.bmm(A3, B3, out=C3), iters=8, warm=1)
+    to = timed(lambda: comm.bmm_allreduce_p2p(A3, B3, sharedC, bestp["panels"]), iters=8, warm=1)
+    prounds.append({"gemm_only_ms": tg, "p2p_ms": to, "weak_eff": tg / to})
+bp["gemm_per_iter"] = timed_each(lambda: b2.bmm(A3, B3, out=C3))
+bp["nccl_overlap_per_iter"] = timed_each(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, best["panels"]))
+bp["p2p_best"] = bestp
+bp["p2p_interleaved_rounds"] = prounds
+bp["p2p_weak_scaling_eff"] = sum(r["weak_eff"] for r in prounds) / len(prounds)
+# parity of the p2p pipeline against NCCL's all_reduce of the same product
+comm.bmm_allreduce_p2p(A3, B3, sharedC, 4)
+b2.bmm(A3, B3, out=C3)
+comm.all_reduce(C3)
+torch.cuda.synchronize()
+ref = C3[0, :256].double()
+bp["p2p_vs_nccl_err"] = max_ranks(((sharedC.local[0, :256].double() - ref).abs() / (ref.abs() + ref.pow(2).mean().sqrt())).max().item())
 bp["best"] = best
 bp["interleaved_rounds"] = rounds
 bp["weak_scaling_eff"] = sum(r["weak_eff"] for r in rounds) / len(rounds)

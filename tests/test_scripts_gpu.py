@@ -48,7 +48,8 @@ def test_scaling_script_single_gpu_all_modes(dtype):
 @pytest.mark.parametrize("mode,extra", [("independent", []), ("batch_parallel", []), ("matrix_parallel", []),
                                         ("batch_parallel", ["--overlap", "--panels", "2"]),
                                         ("matrix_parallel", ["--overlap", "--panels", "4"]),
-                                        ("matrix_parallel", ["--fused"])])
+                                        ("matrix_parallel", ["--fused"]),
+                                        ("batch_parallel", ["--fused", "--panels", "2"])])
 def test_scaling_script_two_gpus(mode, extra):
     out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                 "--master-addr=127.0.0.1", f"--master-port={_free_port()}", "matmul_scaling_benchmark.py", "--sizes",
@@ -59,4 +60,4 @@ def test_scaling_script_two_gpus(mode, extra):
     if "--overlap" in extra:
         assert "Overlapped end-to-end:" in out
     if "--fused" in extra:
-        assert "Fused GEMM+all_gather end-to-end:" in out
+        assert "Fused GEMM+all_" in out and out.count("-> OK") >= 2

@@ -15,8 +15,9 @@ Prints ONE JSON line (rank 0).  Keys beyond the base contract:
                 capture (profiles/roofline_traffic.json) or null.
   cpu_baseline  the reference's CPU path (torch.matmul on CPU, timed as matmul_benchmark.py:69-74
                 does; restated in oracle/reference_port.py) on the box's host cores, bounded sample.
-  e2e           the same metric through the public API with HOST buffers: every step copies A and B
-                from pinned host memory, runs the GEMM, and copies C back.
+  e2e           the same metric through the public host-buffer call (ops.HostGemm): every step copies A
+                and B from pinned host memory, runs the GEMM and copies C back — all inside the timed
+                region; within a step the row panels of A/C are pipelined against the math.
 
 `--impl reference` times the reference's CPU implementation (the port above; the reference is pure
 Python over torch and cannot travel to the GPU box) with all host threads; each step is a bounded
@@ -54,7 +55,7 @@ def measured_peaks() -> dict:
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the warm-up + timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -62,7 +63,7 @@ class ClockSampler:
         self.lines, self.proc, self.thread = [], None, None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms",
-                                          "100", "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "50", "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
         except OSError:
@@ -177,12 +178,12 @@ def run_b2mm(args) -> None:
     sampler = ClockSampler(dev.index) if rank == 0 else None
 
     def timed_device_region():
+        w0 = time.time()  # clocks are sampled from the first warm-up launch on: same kernel, same load
         for _ in range(args.warmup):
             b2.matmul(A, B, out=C)
         barrier()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
         launches0 = _lib.launch_count()
-        w0 = time.time()
         ev[0].record(stream)
         for i in range(args.steps):
             b2.matmul(A, B, out=C)
@@ -211,14 +212,12 @@ def run_b2mm(args) -> None:
     hC = torch.empty(N, N, dtype=torch.bfloat16, pin_memory=True)
     hA.copy_(A)
     hB.copy_(B)
-    dA, dB, dC = torch.empty_like(A), torch.empty_like(B), torch.empty_like(C)
+    del C
+    host_gemm = b2.HostGemm(N, N, N, torch.bfloat16, device=dev, panels=8)  # the public host-buffer call
     e2e_steps = max(3, min(args.steps, 10))
 
     def e2e_step():
-        dA.copy_(hA, non_blocking=True)
-        dB.copy_(hB, non_blocking=True)
-        b2.matmul(dA, dB, out=dC)
-        hC.copy_(dC, non_blocking=True)
+        host_gemm(hA, hB, hC)
 
     for _ in range(2):
         e2e_step()

@@ -5,6 +5,6 @@ Host-side mirror of the reference's operators over the C-ABI library
 library; the first operator call does, and fails loudly if it is not built.
 """
 from . import _lib  # noqa: F401
-from .ops import Communicator, bmm, matmul, release_workspaces  # noqa: F401
+from .ops import Communicator, HostGemm, bmm, matmul, release_workspaces  # noqa: F401
 
-__all__ = ["matmul", "bmm", "Communicator", "release_workspaces"]
+__all__ = ["matmul", "bmm", "HostGemm", "Communicator", "release_workspaces"]

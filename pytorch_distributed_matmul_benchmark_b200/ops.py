@@ -127,6 +127,57 @@ def bmm(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None) ->
     return out
 
 
+class HostGemm:
+    """C = A @ B for operands that live in (pinned) HOST memory: the end-to-end call.
+
+    The transfers are pipelined with the math inside one call: B goes up first, then A in row
+    panels; the GEMM of panel i starts as soon as panel i has landed, and its rows of C go back
+    down while panel i+1 is still arriving (PCIe is full duplex).  Device staging buffers, three
+    streams and the events are owned by this object and reused from call to call.
+    """
+
+    def __init__(self, M: int, N: int, K: int, dtype: torch.dtype, device="cuda", panels: int = 8):
+        if M % panels:
+            raise RuntimeError(f"M={M} must be divisible by panels={panels}")
+        self.M, self.N, self.K, self.dtype, self.panels = M, N, K, dtype, panels
+        self.device = torch.device(device)
+        self.dA = torch.empty(M, K, dtype=dtype, device=self.device)
+        self.dB = torch.empty(K, N, dtype=dtype, device=self.device)
+        self.dC = torch.empty(M, N, dtype=dtype, device=self.device)
+        self.up = torch.cuda.Stream(device=self.device)
+        self.down = torch.cuda.Stream(device=self.device)
+        self.ev_b = torch.cuda.Event()
+        self.ev_a = [torch.cuda.Event() for _ in range(panels)]
+        self.ev_c = [torch.cuda.Event() for _ in range(panels)]
+        self.ev_done = torch.cuda.Event()
+
+    def __call__(self, hA: torch.Tensor, hB: torch.Tensor, hC: torch.Tensor) -> torch.Tensor:
+        for t in (hA, hB, hC):
+            if t.is_cuda or not t.is_pinned():
+                raise RuntimeError("HostGemm takes pinned host tensors")
+        main = torch.cuda.current_stream(self.device)
+        rows = self.M // self.panels
+        self.up.wait_stream(main)    # the previous call's GEMMs no longer read dA / dB
+        self.down.wait_stream(main)
+        with torch.cuda.stream(self.up):
+            self.dB.copy_(hB, non_blocking=True)
+            self.ev_b.record()
+            for i in range(self.panels):
+                self.dA[i * rows:(i + 1) * rows].copy_(hA[i * rows:(i + 1) * rows], non_blocking=True)
+                self.ev_a[i].record()
+        main.wait_event(self.ev_b)
+        for i in range(self.panels):
+            main.wait_event(self.ev_a[i])
+            matmul(self.dA[i * rows:(i + 1) * rows], self.dB, out=self.dC[i * rows:(i + 1) * rows])
+            self.ev_c[i].record(main)
+            with torch.cuda.stream(self.down):
+                self.down.wait_event(self.ev_c[i])
+                hC[i * rows:(i + 1) * rows].copy_(self.dC[i * rows:(i + 1) * rows], non_blocking=True)
+        self.ev_done.record(self.down)
+        main.wait_event(self.ev_done)  # on the caller's stream, the call is complete when hC is
+        return hC
+
+
 class SharedSlabs:
     """A rank's gather buffer plus the pointers under which every rank's buffer is visible here."""
 

@@ -194,3 +194,21 @@ def test_bmm_matches_per_matrix_matmul_and_oracle():
     for b in range(3):
         assert torch.equal(C[b], b2.matmul(A[b], B[b]))
     assert rel_err(C[1], oracle.gemm_block_f64(A[1].cpu(), B[1].cpu(), 0, 520, 0, 776)) <= TOL[torch.bfloat16]
+
+
+def test_host_gemm_pipelined_transfers_match_device_path():
+    """ops.HostGemm (pinned host operands, panel-pipelined copies) gives the bits of the device-resident call."""
+    torch.manual_seed(21)
+    M, N, K = 1024, 776, 520
+    hA = torch.randn(M, K, dtype=torch.bfloat16).pin_memory()
+    hB = torch.randn(K, N, dtype=torch.bfloat16).pin_memory()
+    hC = torch.empty(M, N, dtype=torch.bfloat16).pin_memory()
+    g = b2.HostGemm(M, N, K, torch.bfloat16, device=DEV, panels=4)
+    for _ in range(2):  # second call reuses the staging buffers and events
+        hC.zero_()
+        g(hA, hB, hC)
+        torch.cuda.synchronize()
+        assert torch.equal(hC, b2.matmul(hA.to(DEV), hB.to(DEV)).cpu())
+    assert rel_err(hC, oracle.gemm_block_f64(hA, hB, 0, M, 0, N)) <= TOL[torch.bfloat16]
+    with pytest.raises(RuntimeError, match="pinned"):
+        g(torch.zeros(M, K, dtype=torch.bfloat16), hB, hC)

@@ -223,6 +223,19 @@ B2MM_API int b2mm_gemm_allreduce_p2p(void* comm, const void* A, const void* B, v
                                      b2mm_stream_t compute, b2mm_stream_t comm_stream);
 
 /*
+ * batch_parallel with the reduction fused next to the GEMM (matmul_scaling_benchmark.py:142 + :150): like
+ * b2mm_gemm_allreduce_p2p, but the reduction kernels carry their own cross-GPU synchronisation (epoch
+ * counters in peer-mapped signal pads) and are built to be CO-RESIDENT with the GEMM's CTAs — no shared
+ * memory, few registers — so the reduction of panel i runs on the same SMs as the GEMM of panel i+1 and
+ * the GEMM keeps the whole device and its dynamic scheduler.  No NCCL kernel on the path.
+ *   peer_signals[r]: rank r's signal pad, int32[16], zero-initialised once, mapped like peer_C.
+ */
+B2MM_API int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* const* peer_C,
+                                       void* const* peer_signals, int64_t N, int64_t local_batch, int dtype,
+                                       int n_panels, void* workspace, size_t workspace_bytes,
+                                       b2mm_stream_t compute, b2mm_stream_t comm_stream);
+
+/*
  * matrix_parallel with the gather pipelined behind compute
  * (after backup/matmul_overlap_benchmark.py:93-180, made race-free):
  * C_local = A * B_local is computed in `n_panels` row panels on `compute`;

@@ -12,6 +12,8 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+#include <cstdio>
+
 namespace b2mm {
 
 struct PeerPtrs {
@@ -111,6 +113,110 @@ __global__ void __launch_bounds__(512) allreduce_p2p_kernel(PeerPtrs ptrs, int w
         }
       }
     }
+  }
+}
+
+// ---- the same reduction with its cross-GPU synchronisation inside the kernel -----------------
+// Signal pads: every rank owns int32[16] in peer-mapped memory: [0, 8) "panel ready" epochs and
+// [8, 16) "pushes done" epochs, one slot per source rank, written by that rank over NVLink.
+// Counters only grow, so nothing is ever reset.
+struct SignalPtrs {
+  int* p[8];
+};
+
+__device__ __forceinline__ void st_release_sys(int* addr, int v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int* addr) {
+  int v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+// Spin until *addr >= epoch; a peer that never shows up traps instead of hanging the GPU.
+__device__ __forceinline__ void wait_epoch(const int* addr, int epoch) {
+  const long long t0 = clock64();
+  while (ld_acquire_sys(addr) - epoch < 0) {
+    if (clock64() - t0 > 20000000000ll) {
+      printf("b2mm: peer signal watchdog (block %d thread %d, want %d, have %d)\n", (int)blockIdx.x, (int)threadIdx.x, epoch,
+             ld_acquire_sys(addr));
+      __trap();
+    }
+  }
+}
+
+// Needs no shared memory and few registers on purpose: its CTAs are meant to be co-resident with the
+// GEMM's (which own all of an SM's shared memory but few of its threads), so the reduction of panel i
+// runs on the same SMs as the GEMM of panel i+1 and nothing has to be reserved for it.
+template <typename T, int kUnroll>
+__global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(PeerPtrs ptrs, SignalPtrs sig, int rank, int world, int epoch,
+                                                                  int64_t vec_begin, int64_t vec_count) {
+  if ((int)threadIdx.x < world) {
+    if (blockIdx.x == 0) st_release_sys(sig.p[threadIdx.x] + rank, epoch);  // my panel is complete (kernel order)
+    wait_epoch(sig.p[rank] + threadIdx.x, epoch);                           // ... and so is everybody else's
+  }
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  constexpr int kLanes = sizeof(T) == 4 ? 4 : 8;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < vec_count; base += stride * kUnroll) {
+    float acc[kUnroll][kLanes];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+      for (int j = 0; j < kLanes; ++j) acc[u][j] = 0.f;
+    for (int r = 0; r < world; ++r) {
+      const uint4* src = reinterpret_cast<const uint4*>(ptrs.p[r]) + vec_begin;
+      uint4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + u * stride;
+        if (i < vec_count) asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i));
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (base + u * stride < vec_count) {
+          if constexpr (sizeof(T) == 4) {
+            acc[u][0] += __uint_as_float(v[u].x);
+            acc[u][1] += __uint_as_float(v[u].y);
+            acc[u][2] += __uint_as_float(v[u].z);
+            acc[u][3] += __uint_as_float(v[u].w);
+          } else {
+            float f[8];
+            unpack8<T>(v[u], f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[u][j] += f[j];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + u * stride;
+      if (i < vec_count) {
+        uint4 out;
+        if constexpr (sizeof(T) == 4) {
+          out = make_uint4(__float_as_uint(acc[u][0]), __float_as_uint(acc[u][1]), __float_as_uint(acc[u][2]), __float_as_uint(acc[u][3]));
+        } else {
+          float f[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = acc[u][j];
+          out = pack8<T>(f);
+        }
+        for (int d = 0; d < world; ++d) {
+          uint4* dst = reinterpret_cast<uint4*>(ptrs.p[d]) + vec_begin + i;
+          asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(out.x), "r"(out.y), "r"(out.z), "r"(out.w) : "memory");
+        }
+      }
+    }
+  }
+}
+
+// After the last reduction of a call: tell every rank that this rank's pushes have landed, then wait for
+// the same from every rank.  One warp.
+__global__ void p2p_done_kernel(SignalPtrs sig, int rank, int world, int epoch) {
+  if ((int)threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(sig.p[threadIdx.x] + 8 + rank, epoch);
+    wait_epoch(sig.p[rank] + 8 + threadIdx.x, epoch);
   }
 }
 

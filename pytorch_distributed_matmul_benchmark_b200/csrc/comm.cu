@@ -21,6 +21,7 @@ struct NcclApi {
   void* handle = nullptr;
   ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommInitRankConfig)(ncclComm_t*, int, ncclUniqueId, int, ncclConfig_t*) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -54,6 +55,7 @@ static NcclApi& nccl() {
     B2MM_SYM(GroupEnd, "ncclGroupEnd")
     B2MM_SYM(GetErrorString, "ncclGetErrorString")
 #undef B2MM_SYM
+    api.CommInitRankConfig = reinterpret_cast<decltype(api.CommInitRankConfig)>(dlsym(api.handle, "ncclCommInitRankConfig"));
     api.ok = true;
   });
   return api;
@@ -67,6 +69,8 @@ struct Comm {
   cudaEvent_t panel_done[kMaxPanels];
   cudaEvent_t comm_done = nullptr;
   float* barrier_word = nullptr;  // 1 float on the device: payload of b2mm_comm_barrier
+  int ready_epoch = 0;            // fused all_reduce: panels announced so far (same sequence on every rank)
+  int done_epoch = 0;             // fused all_reduce: calls completed so far
 };
 
 static int nccl_fail(const char* what, ncclResult_t r) {
@@ -126,7 +130,20 @@ int b2mm_comm_init(const void* id_bytes, int rank, int world, void** comm_out) {
   Comm* c = new Comm();
   c->rank = rank;
   c->world = world;
-  ncclResult_t r = nccl().CommInitRank(&c->nccl, world, id, rank);
+  // B2MM_NCCL_MAX_CTAS=n caps the CTAs NCCL's kernels use on this communicator: in the pipelined modes
+  // they run beside a GEMM that leaves only a few SMs free, and a collective that cannot get all of
+  // its CTAs resident at once waits for the GEMM panel to finish.
+  const char* mc = getenv("B2MM_NCCL_MAX_CTAS");
+  const int max_ctas = (mc && *mc) ? atoi(mc) : 0;
+  ncclResult_t r;
+  if (max_ctas > 0 && nccl().CommInitRankConfig) {
+    ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+    cfg.maxCTAs = max_ctas;
+    cfg.minCTAs = 1;
+    r = nccl().CommInitRankConfig(&c->nccl, world, id, rank, &cfg);
+  } else {
+    r = nccl().CommInitRank(&c->nccl, world, id, rank);
+  }
   if (r != ncclSuccess) {
     delete c;
     return nccl_fail("ncclCommInitRank", r);
@@ -340,6 +357,62 @@ int b2mm_gemm_allreduce_p2p(void* comm, const void* A, const void* B, void* cons
     }
   }
   if ((rc = b2mm_comm_barrier(comm, cs))) return rc;  // all pushes have landed everywhere
+  if (cudaEventRecord(c->comm_done, cs) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
+  if (cudaStreamWaitEvent(compute, c->comm_done, 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
+  return B2MM_OK;
+}
+
+int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* const* peer_C, void* const* peer_signals,
+                              int64_t N, int64_t local_batch, int dtype, int n_panels, void* workspace,
+                              size_t workspace_bytes, b2mm_stream_t compute_, b2mm_stream_t comm_stream_) {
+  Comm* c = (Comm*)comm;
+  if (!c || !peer_C || !peer_signals || !dtype_bytes(dtype) || c->world > 8) return fail(B2MM_ERR_BAD_ARG, "bad comm, dtype or buffer list");
+  if (local_batch == 0) return B2MM_OK;
+  if (n_panels < 1 || n_panels * local_batch > kMaxPanels)
+    return fail(B2MM_ERR_BAD_ARG, "n_panels * local_batch must be in [1, %d]", kMaxPanels);
+  if (N % n_panels) return fail(B2MM_ERR_UNSUPPORTED, "N=%lld is not divisible by n_panels=%d", (long long)N, n_panels);
+  cudaStream_t compute = (cudaStream_t)compute_, cs = (cudaStream_t)comm_stream_;
+  const int es = dtype_bytes(dtype);
+  const int64_t mp = N / n_panels;
+  if ((mp * N * es) % (16 * c->world)) return fail(B2MM_ERR_UNSUPPORTED, "panel size is not a multiple of 16 bytes x world");
+  PeerPtrs pp;
+  SignalPtrs sp;
+  for (int d = 0; d < 8; ++d) {
+    pp.p[d] = peer_C[d < c->world ? d : 0];
+    sp.p[d] = (int*)peer_signals[d < c->world ? d : 0];
+  }
+  const char* v = getenv("B2MM_P2P_CTAS");
+  int ctas = (v && *v) ? atoi(v) : device_sm_count();  // one per SM, beside the GEMM's CTA
+  if (ctas < 1) ctas = 1;
+  constexpr int kUnroll = 4;
+  char* C = (char*)peer_C[c->rank];
+  int ev = 0, rc;
+  for (int64_t b = 0; b < local_batch; ++b) {
+    for (int i = 0; i < n_panels; ++i, ++ev) {
+      const int64_t elem_off = b * N * N + (int64_t)i * mp * N;
+      const char* a = (const char*)A + (size_t)elem_off * es;
+      const char* bb = (const char*)B + (size_t)b * N * N * es;
+      // full-device GEMM, dynamic scheduler: nothing is reserved for the reduction
+      if ((rc = gemm_impl(a, bb, C + (size_t)elem_off * es, mp, N, N, N, N, N, 1, 0, 0, 0, dtype, workspace, workspace_bytes, compute)))
+        return rc;
+      if (cudaEventRecord(c->panel_done[ev], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
+      if (cudaStreamWaitEvent(cs, c->panel_done[ev], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
+      const int64_t vecs = mp * N * es / 16, per = vecs / c->world;
+      const int64_t begin = elem_off * es / 16 + per * c->rank;
+      const int epoch = ++c->ready_epoch;
+      switch (dtype) {
+        case B2MM_BF16: allreduce_p2p_sync_kernel<__nv_bfloat16, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per); break;
+        case B2MM_FP16: allreduce_p2p_sync_kernel<__half, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per); break;
+        default: allreduce_p2p_sync_kernel<float, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per); break;
+      }
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "fused all_reduce launch failed: %s", cudaGetErrorString(e));
+      count_launch(1);
+    }
+  }
+  p2p_done_kernel<<<1, 32, 0, cs>>>(sp, c->rank, c->world, ++c->done_epoch);
+  if (cudaGetLastError() != cudaSuccess) return fail(B2MM_ERR_CUDA, "done-signal launch failed");
+  count_launch(1);
   if (cudaEventRecord(c->comm_done, cs) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
   if (cudaStreamWaitEvent(compute, c->comm_done, 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
   return B2MM_OK;

@@ -98,7 +98,7 @@ class Ops:
     shared_slabs: Optional[Callable] = None  # (M, n_local, dtype) -> SharedSlabs
     matmul_allgather_fused: Optional[Callable] = None  # (A, B_local, shared) -> slabs
     shared_like: Optional[Callable] = None  # (t) -> SharedSlabs
-    bmm_allreduce_p2p: Optional[Callable] = None  # (A, B, shared_C, n_panels) -> C
+    bmm_allreduce_fused: Optional[Callable] = None  # (A, B, shared_C, n_panels) -> C
     synchronize: Callable = torch.cuda.synchronize
     event: Callable = lambda: torch.cuda.Event(enable_timing=True)
     destroy: Callable = lambda: None
@@ -122,7 +122,7 @@ def device_ops(rank: int, world_size: int, device: str) -> Ops:
         shared_slabs=comm.shared_slabs if comm else None,
         matmul_allgather_fused=comm.matmul_allgather_fused if comm else None,
         shared_like=comm.shared_like if comm else None,
-        bmm_allreduce_p2p=comm.bmm_allreduce_p2p if comm else None,
+        bmm_allreduce_fused=comm.bmm_allreduce_fused if comm else None,
         destroy=comm.destroy if comm else (lambda: None),
     )
 

@@ -10,9 +10,10 @@ Additive behaviour (flags the reference does not have):
                    both the reference-style serial split and the end-to-end time are reported
   --panels P       row panels per GEMM in --overlap mode
   --fused          matrix_parallel: ONE kernel whose epilogue stores each C tile into every rank's gather
-                   buffer over NVLink (no collective kernel).  batch_parallel: row-panel pipeline of the
-                   library's own kernels — GEMM panels, then a peer-memory all-reduce (pull, fp32 add,
-                   push) behind each panel.  Reported like --overlap
+                   buffer over NVLink (no collective kernel).  batch_parallel: GEMM row panels on the
+                   whole device, each followed by the library's own peer-memory all-reduce (pull, fp32
+                   add, push; self-synchronising, co-resident with the next panel's GEMM).  No NCCL kernel
+                   on either path.  Reported like --overlap
   --batch-size B   total batch for batch_parallel (reference: 4, hard-coded at :283)
   --per-gpu-batch  fixed local batch per GPU (weak scaling; the reference's 4 // ws is 0 at ws=8)
 """
@@ -160,13 +161,13 @@ def benchmark_batch_parallel(matrix_size: int, batch_size: int, dtype: torch.dty
             print(f"    Overlapped end-to-end: {avg_overlap*1000:.3f} ms ({panels} panels; serial sum {avg_total_time*1000:.3f} ms)")
         avg_total_time = avg_overlap
 
-    if fused and comm_on and local_batch_size > 0 and ops.bmm_allreduce_p2p is not None:
+    if fused and comm_on and local_batch_size > 0 and ops.bmm_allreduce_fused is not None:
         shared = ops.shared_like(C)
         for _ in range(min(warmup_iterations, 3)):
-            ops.bmm_allreduce_p2p(A, B, shared, panels)
+            ops.bmm_allreduce_fused(A, B, shared, panels)
         ops.synchronize()
         dist.barrier()
-        avg_fused = _timed_loop(ops, lambda: ops.bmm_allreduce_p2p(A, B, shared, panels), num_iterations)
+        avg_fused = _timed_loop(ops, lambda: ops.bmm_allreduce_fused(A, B, shared, panels), num_iterations)
         if rank == 0:
             print(f"    Fused GEMM+all_reduce (peer memory) end-to-end: {avg_fused*1000:.3f} ms ({panels} panels; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
         if check:  # against the NCCL all_reduce of the same product: two roundings of one sum, at most ~1 ulp apart

@@ -295,6 +295,23 @@ class Communicator:
             ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(), self.comm_stream.cuda_stream))
         return shared_C.local
 
+    def bmm_allreduce_fused(self, A: torch.Tensor, B: torch.Tensor, shared_C: "SharedSlabs", n_panels: int = 4) -> torch.Tensor:
+        """C = bmm(A, B) in row panels; each panel summed over ranks by a self-synchronising peer-memory kernel
+        that shares the SMs with the next panel's GEMM (no NCCL, nothing reserved)."""
+        _require_cuda(A, B)
+        if getattr(self, "_signals", None) is None:
+            pad = torch.zeros(64, dtype=torch.int32, device=self.device)
+            torch.cuda.synchronize(self.device)
+            self._signals = self.share(pad)
+        b, N, _ = A.shape
+        code = _dtype_code(A)
+        ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)
+        self.comm_stream.wait_stream(torch.cuda.current_stream())
+        _lib.check(_lib.load().b2mm_gemm_allreduce_fused(
+            self._comm, A.data_ptr(), B.data_ptr(), shared_C.peer_ptrs, self._signals.peer_ptrs, N, b, code, n_panels,
+            ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(), self.comm_stream.cuda_stream))
+        return shared_C.local
+
     def matmul_allgather_fused(self, A: torch.Tensor, B_local: torch.Tensor, shared: "SharedSlabs") -> torch.Tensor:
         """C_local = A @ B_local with the all_gather done by the GEMM epilogue (peer TMA stores), then a barrier."""
         _require_cuda(A, B_local)

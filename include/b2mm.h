@@ -223,17 +223,21 @@ B2MM_API int b2mm_gemm_allreduce_p2p(void* comm, const void* A, const void* B, v
                                      b2mm_stream_t compute, b2mm_stream_t comm_stream);
 
 /*
- * batch_parallel with the reduction fused next to the GEMM (matmul_scaling_benchmark.py:142 + :150): like
- * b2mm_gemm_allreduce_p2p, but the reduction kernels carry their own cross-GPU synchronisation (epoch
- * counters in peer-mapped signal pads) and are built to be CO-RESIDENT with the GEMM's CTAs — no shared
- * memory, few registers — so the reduction of panel i runs on the same SMs as the GEMM of panel i+1 and
- * the GEMM keeps the whole device and its dynamic scheduler.  No NCCL kernel on the path.
+ * batch_parallel with the reduction fused next to the GEMM (matmul_scaling_benchmark.py:142 + :150).
+ * ONE GEMM over the whole local batch runs on the whole device; its epilogues count finished tiles per
+ * row band (N / n_bands rows).  The reductions, one kernel per band, are queued at the same time on
+ * `comm_stream`; their CTAs use no shared memory and few registers so that they are CO-RESIDENT with the
+ * GEMM's CTAs: each waits on the device for its band, then for the same band on every rank (epoch counters
+ * in peer-mapped signal pads), then pulls / adds in fp32 / pushes as b2mm_all_reduce_p2p.  No NCCL kernel,
+ * nothing reserved, no panel launches.
  *   peer_signals[r]: rank r's signal pad, int32[16], zero-initialised once, mapped like peer_C.
+ *   band_counters:   local scratch, int32[n_bands * local_batch] (cleared by the call).
+ *   band rows must be a multiple of the GEMM's tile height (512).
  */
 B2MM_API int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* const* peer_C,
-                                       void* const* peer_signals, int64_t N, int64_t local_batch, int dtype,
-                                       int n_panels, void* workspace, size_t workspace_bytes,
-                                       b2mm_stream_t compute, b2mm_stream_t comm_stream);
+                                       void* const* peer_signals, int* band_counters, int64_t N,
+                                       int64_t local_batch, int dtype, int n_bands, void* workspace,
+                                       size_t workspace_bytes, b2mm_stream_t compute, b2mm_stream_t comm_stream);
 
 /*
  * matrix_parallel with the gather pipelined behind compute

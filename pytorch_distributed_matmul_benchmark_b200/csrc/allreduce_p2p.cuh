@@ -149,7 +149,22 @@ __device__ __forceinline__ void wait_epoch(const int* addr, int epoch) {
 // runs on the same SMs as the GEMM of panel i+1 and nothing has to be reserved for it.
 template <typename T, int kUnroll>
 __global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(PeerPtrs ptrs, SignalPtrs sig, int rank, int world, int epoch,
-                                                                  int64_t vec_begin, int64_t vec_count) {
+                                                                  int64_t vec_begin, int64_t vec_count,
+                                                                  const int* band_counter, int band_target) {
+  if (band_counter != nullptr && threadIdx.x == 0) {
+    // Launched next to the GEMM that produces the data: wait until the GEMM's epilogues have published
+    // this row band (GemmParams::band_counter) before telling the other ranks that it is ready.
+    const long long t0 = clock64();
+    int seen;
+    do {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(band_counter) : "memory");
+      if (clock64() - t0 > 20000000000ll) {
+        printf("b2mm: band watchdog (block %d, want %d, have %d)\n", (int)blockIdx.x, band_target, seen);
+        __trap();
+      }
+    } while (seen < band_target);
+  }
+  if (band_counter != nullptr) __syncthreads();
   if ((int)threadIdx.x < world) {
     if (blockIdx.x == 0) st_release_sys(sig.p[threadIdx.x] + rank, epoch);  // my panel is complete (kernel order)
     wait_epoch(sig.p[rank] + threadIdx.x, epoch);                           // ... and so is everybody else's

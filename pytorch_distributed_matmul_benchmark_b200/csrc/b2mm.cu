@@ -107,6 +107,9 @@ struct Operands {
   void* const* fan_ptrs;  // fanout destinations for C (null: just C)
   int fanout;
   int tiles_per_cluster;
+  int* band_counter;
+  int band_rows;
+  const GemmOpts* opts;
 };
 
 template <class Cfg>
@@ -164,6 +167,17 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   p.trace = g_trace;
   p.fanout = o.fanout;
   p.max_tiles = o.tiles_per_cluster;
+  p.band_counter = o.band_counter;
+  p.band_tiles = 1;
+  p.bands_per_batch = 1;
+  if (o.band_counter) {
+    if (o.band_rows % Cfg::TILE_M) return fail(B2MM_ERR_UNSUPPORTED, "band of %d rows is not a whole number of %d-row tiles", o.band_rows, Cfg::TILE_M);
+    p.band_tiles = o.band_rows / Cfg::TILE_M;
+    p.bands_per_batch = (p.m_tiles + p.band_tiles - 1) / p.band_tiles;
+    p.group_m = p.band_tiles;  // the raster band IS the signalling band: bands complete in order
+    o.opts->signals_per_band = p.band_tiles * p.n_tiles * Cfg::kCtaGroup * Cfg::kEpiWarps;
+    o.opts->bands_per_batch = p.bands_per_batch;
+  }
   // Dynamic (hardware work-stealing) scheduling unless the caller capped the SMs.
   const char* sched = getenv("B2MM_SCHED");
   p.dynamic = (max_sms > 0 || (sched && !strcmp(sched, "static"))) ? 0 : 1;
@@ -250,7 +264,7 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
     return fail(B2MM_ERR_UNSUPPORTED, "dimension too large");
 
   Operands o{A, B, nullptr, nullptr, C, M, N, K, lda, ldb, ldc, batch, sA, sB, sC, dtype, fan_ptrs, fanout,
-             opts.tiles_per_cluster};
+             opts.tiles_per_cluster, opts.band_counter, opts.band_rows, &opts};
   const int sms = device_sm_count();
   int clusters = (max_sms > 0 && max_sms < sms ? max_sms : sms) / 2;
   if (clusters < 1) clusters = 1;

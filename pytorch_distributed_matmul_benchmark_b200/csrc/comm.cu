@@ -363,47 +363,71 @@ int b2mm_gemm_allreduce_p2p(void* comm, const void* A, const void* B, void* cons
 }
 
 int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* const* peer_C, void* const* peer_signals,
-                              int64_t N, int64_t local_batch, int dtype, int n_panels, void* workspace,
+                              int* band_counters, int64_t N, int64_t local_batch, int dtype, int n_bands, void* workspace,
                               size_t workspace_bytes, b2mm_stream_t compute_, b2mm_stream_t comm_stream_) {
   Comm* c = (Comm*)comm;
-  if (!c || !peer_C || !peer_signals || !dtype_bytes(dtype) || c->world > 8) return fail(B2MM_ERR_BAD_ARG, "bad comm, dtype or buffer list");
+  if (!c || !peer_C || !peer_signals || !band_counters || !dtype_bytes(dtype) || c->world > 8)
+    return fail(B2MM_ERR_BAD_ARG, "bad comm, dtype or buffer list");
   if (local_batch == 0) return B2MM_OK;
-  if (n_panels < 1 || n_panels * local_batch > kMaxPanels)
-    return fail(B2MM_ERR_BAD_ARG, "n_panels * local_batch must be in [1, %d]", kMaxPanels);
-  if (N % n_panels) return fail(B2MM_ERR_UNSUPPORTED, "N=%lld is not divisible by n_panels=%d", (long long)N, n_panels);
+  if (n_bands < 1 || n_bands * local_batch > kMaxPanels)
+    return fail(B2MM_ERR_BAD_ARG, "n_bands * local_batch must be in [1, %d]", kMaxPanels);
+  if (N % n_bands) return fail(B2MM_ERR_UNSUPPORTED, "N=%lld is not divisible by n_bands=%d", (long long)N, n_bands);
   cudaStream_t compute = (cudaStream_t)compute_, cs = (cudaStream_t)comm_stream_;
   const int es = dtype_bytes(dtype);
-  const int64_t mp = N / n_panels;
-  if ((mp * N * es) % (16 * c->world)) return fail(B2MM_ERR_UNSUPPORTED, "panel size is not a multiple of 16 bytes x world");
+  const int64_t band_rows = N / n_bands;
+  if ((band_rows * N * es) % (16 * c->world)) return fail(B2MM_ERR_UNSUPPORTED, "band size is not a multiple of 16 bytes x world");
   PeerPtrs pp;
   SignalPtrs sp;
   for (int d = 0; d < 8; ++d) {
     pp.p[d] = peer_C[d < c->world ? d : 0];
     sp.p[d] = (int*)peer_signals[d < c->world ? d : 0];
   }
+  // Fewer CTAs than SMs on purpose: should the reduction's CTAs ever fail to share SMs with the GEMM's, the
+  // GEMM still finds free SMs and the wait below ends (slowly) instead of deadlocking.
   const char* v = getenv("B2MM_P2P_CTAS");
-  int ctas = (v && *v) ? atoi(v) : device_sm_count();  // one per SM, beside the GEMM's CTA
+  int ctas = (v && *v) ? atoi(v) : device_sm_count() - 8;
   if (ctas < 1) ctas = 1;
   constexpr int kUnroll = 4;
-  char* C = (char*)peer_C[c->rank];
-  int ev = 0, rc;
+  {
+    // CTAs of two kernels share an SM only if both ask for the same L1/shared-memory split: the GEMM runs
+    // with the maximum shared-memory carve-out, so the (shared-memory-free) reduction asks for it too.
+    static std::once_flag once[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64)
+      std::call_once(once[dev], [] {
+        const int co = cudaSharedmemCarveoutMaxShared;
+        cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__nv_bfloat16, kUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+        cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__half, kUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+        cudaFuncSetAttribute(allreduce_p2p_sync_kernel<float, kUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+        cudaFuncSetAttribute(p2p_done_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+      });
+  }
+  // compute: clear the progress counters, then ONE GEMM over the whole batch on the whole device; its
+  // epilogues count finished tiles per row band.
+  const int total_bands = (int)(n_bands * local_batch);
+  if (cudaMemsetAsync(band_counters, 0, sizeof(int) * total_bands, compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "memset failed");
+  if (cudaEventRecord(c->panel_done[0], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
+  if (cudaStreamWaitEvent(cs, c->panel_done[0], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
+  GemmOpts opts;
+  opts.band_counter = band_counters;
+  opts.band_rows = (int)band_rows;
+  int rc = gemm_impl(A, B, peer_C[c->rank], N, N, N, N, N, N, local_batch, N * N, N * N, N * N, dtype, workspace, workspace_bytes,
+                     compute, opts);
+  if (rc) return rc;
+  if (opts.bands_per_batch != n_bands) return fail(B2MM_ERR_UNSUPPORTED, "band geometry mismatch (%d vs %d)", opts.bands_per_batch, n_bands);
+  // comm: one reduction per band, queued now, each waiting (on the device) for its band, then for its peers.
   for (int64_t b = 0; b < local_batch; ++b) {
-    for (int i = 0; i < n_panels; ++i, ++ev) {
-      const int64_t elem_off = b * N * N + (int64_t)i * mp * N;
-      const char* a = (const char*)A + (size_t)elem_off * es;
-      const char* bb = (const char*)B + (size_t)b * N * N * es;
-      // full-device GEMM, dynamic scheduler: nothing is reserved for the reduction
-      if ((rc = gemm_impl(a, bb, C + (size_t)elem_off * es, mp, N, N, N, N, N, 1, 0, 0, 0, dtype, workspace, workspace_bytes, compute)))
-        return rc;
-      if (cudaEventRecord(c->panel_done[ev], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
-      if (cudaStreamWaitEvent(cs, c->panel_done[ev], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
-      const int64_t vecs = mp * N * es / 16, per = vecs / c->world;
+    for (int i = 0; i < n_bands; ++i) {
+      const int64_t elem_off = b * N * N + (int64_t)i * band_rows * N;
+      const int64_t vecs = band_rows * N * es / 16, per = vecs / c->world;
       const int64_t begin = elem_off * es / 16 + per * c->rank;
       const int epoch = ++c->ready_epoch;
+      const int* ctr = band_counters + b * n_bands + i;
       switch (dtype) {
-        case B2MM_BF16: allreduce_p2p_sync_kernel<__nv_bfloat16, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per); break;
-        case B2MM_FP16: allreduce_p2p_sync_kernel<__half, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per); break;
-        default: allreduce_p2p_sync_kernel<float, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per); break;
+        case B2MM_BF16: allreduce_p2p_sync_kernel<__nv_bfloat16, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per, ctr, opts.signals_per_band); break;
+        case B2MM_FP16: allreduce_p2p_sync_kernel<__half, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per, ctr, opts.signals_per_band); break;
+        default: allreduce_p2p_sync_kernel<float, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per, ctr, opts.signals_per_band); break;
       }
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "fused all_reduce launch failed: %s", cudaGetErrorString(e));

@@ -20,6 +20,11 @@ struct GemmOpts {
   void* const* fan_ptrs = nullptr;    // fanout > 0: C is stored to fan_ptrs[0..fanout) (local or peer-mapped)
   int fanout = 0;
   int tiles_per_cluster = 0;          // dynamic scheduler: clusters retire after this many tiles (0 = never)
+  int* band_counter = nullptr;        // progress counters, one per band of `band_rows` rows (see GemmParams)
+  int band_rows = 0;
+  // out: filled by gemm_impl when band_counter is set
+  mutable int signals_per_band = 0;   // value a band's counter reaches when the band is complete
+  mutable int bands_per_batch = 0;
 };
 
 int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,

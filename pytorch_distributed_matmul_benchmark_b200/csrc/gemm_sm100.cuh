@@ -70,6 +70,12 @@ struct GemmParams {
   // Retiring frees its two SMs, which lets pending blocks of a higher-priority stream (the
   // collective of the previous panel) in; the grid's remaining clusters are launched as usual.
   int max_tiles;
+  // Optional progress counters (fused all_reduce): when non-null, every epilogue warp adds 1 to
+  // band_counter[batch * bands_per_batch + m_blk / band_tiles] once its rows of a tile are in global
+  // memory, so a co-resident consumer kernel can start on a row band as soon as the band is complete.
+  int* band_counter;
+  int band_tiles;       // tile rows per band
+  int bands_per_batch;
   // Optional trace buffer (tools only; null in production): per CTA, per tile
   // iteration, the global-timer value at which the producer started the tile.
   unsigned long long* trace;
@@ -490,6 +496,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tma_store_commit();
     };
 
+    // This warp's part of tile (b, m_blk) is complete in global memory: publish it.
+    auto signal_band = [&](int b, int m_blk) {
+      if (p.band_counter == nullptr) return;
+      if (lane == 0) {
+        tma_store_wait<0>();  // the bulk stores have been performed, not merely read out of smem
+        __threadfence();
+        int* ctr = p.band_counter + (size_t)b * p.bands_per_batch + m_blk / p.band_tiles;
+        asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(ctr) : "memory");
+      }
+      __syncwarp();
+    };
+
     // Move this warp's 32 rows of one accumulator (BLOCK_N columns at t_acc) to C, 128 bytes
     // per row at a time; hand the accumulator back (slot) as soon as it has been read.
     auto drain = [&](uint32_t t_acc, int row0, int col0, int b, int slot) {
@@ -600,16 +618,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           buf ^= 1u;
         }
+        signal_band(b, m_blk);
       } else if constexpr (Cfg::kMBlocks == 1) {
         mbar_wait(tfull_bar + 8u * acc, acc_phase);
         tc_fence_after();
         drain(lane_base + (uint32_t)(acc * Cfg::BLOCK_N), row0, col0, b, acc);
+        signal_band(b, m_blk);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       } else {
         mbar_wait(tfull_bar, acc_phase);
         tc_fence_after();
         drain(lane_base, row0, col0, b, 0);                                    // X: rows 0..127 of the slab
         drain(lane_base + (uint32_t)Cfg::BLOCK_N, row0 + 128, col0, b, 1);     // Y: rows 128..255
+        signal_band(b, m_blk);
         acc_phase ^= 1u;
       }
     }

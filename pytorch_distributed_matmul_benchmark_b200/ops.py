@@ -303,12 +303,14 @@ class Communicator:
             pad = torch.zeros(64, dtype=torch.int32, device=self.device)
             torch.cuda.synchronize(self.device)
             self._signals = self.share(pad)
+            self._band_counters = torch.zeros(256, dtype=torch.int32, device=self.device)
         b, N, _ = A.shape
         code = _dtype_code(A)
         ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)
         self.comm_stream.wait_stream(torch.cuda.current_stream())
         _lib.check(_lib.load().b2mm_gemm_allreduce_fused(
-            self._comm, A.data_ptr(), B.data_ptr(), shared_C.peer_ptrs, self._signals.peer_ptrs, N, b, code, n_panels,
+            self._comm, A.data_ptr(), B.data_ptr(), shared_C.peer_ptrs, self._signals.peer_ptrs,
+            self._band_counters.data_ptr(), N, b, code, n_panels,
             ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(), self.comm_stream.cuda_stream))
         return shared_C.local
 

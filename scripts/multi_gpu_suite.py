@@ -82,57 +82,32 @@ t_ar = timed(lambda: comm.all_reduce(C3))
 bytes_ar = C3.numel() * 2
 bp = {"compute_ms": t_gemm, "comm_ms": t_ar, "serial_ms": t_gemm + t_ar, "serial_eff": t1 / (t_gemm + t_ar),
       "allreduce_busbw_GBs": bytes_ar * 2 * (ws - 1) / ws / (t_ar * 1e-3) / 1e9, "overlap": []}
-configs = [("retire", 1, 4), ("retire", 1, 8), ("retire", 2, 8), ("reserve", 16, 8), ("reserve", 8, 8)]
-for kind, val, panels in configs:
-    os.environ.pop("B2MM_COMM_SMS", None)
-    os.environ.pop("B2MM_TILES_PER_CLUSTER", None)
-    os.environ["B2MM_COMM_SMS" if kind == "reserve" else "B2MM_TILES_PER_CLUSTER"] = str(val)
-    t = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, panels))
-    bp["overlap"].append({"scheme": kind, "value": val, "panels": panels, "ms": t, "eff_vs_cold_T1": t1 / t})
-best = min(bp["overlap"], key=lambda r: r["ms"])
-os.environ.pop("B2MM_COMM_SMS", None)
-os.environ.pop("B2MM_TILES_PER_CLUSTER", None)
-os.environ["B2MM_COMM_SMS" if best["scheme"] == "reserve" else "B2MM_TILES_PER_CLUSTER"] = str(best["value"])
-# weak-scaling efficiency measured fairly: the 1-GPU time (GEMM alone, no comm) and the N-GPU time
-# (GEMM + pipelined all_reduce) interleaved in the same thermal state, three rounds
-rounds = []
-for _ in range(3):
-    tg = timed(lambda: b2.bmm(A3, B3, out=C3), iters=8, warm=1)
-    to = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, best["panels"]), iters=8, warm=1)
-    rounds.append({"gemm_only_ms": tg, "overlap_ms": to, "weak_eff": tg / to})
-# the library's own pipeline: GEMM panels + peer-memory all-reduce behind each panel
+# stream-pipelined with NCCL (16 SMs left to NCCL, 8 row panels) and the fused path (one GEMM + co-resident
+# peer-memory reductions per 2048-row band), each measured in rounds interleaved with the GEMM alone so that
+# the weak-scaling efficiency T(1 GPU) / T(N GPUs) compares times taken in the same thermal state
+os.environ["B2MM_COMM_SMS"] = "16"
 sharedC = comm.shared_like(C3)
 t_p2p_alone = timed(lambda: comm.all_reduce_p2p(sharedC))
 bp["p2p_allreduce_alone_ms"] = t_p2p_alone
 bp["p2p_allreduce_busbw_GBs"] = bytes_ar * 2 * (ws - 1) / ws / (t_p2p_alone * 1e-3) / 1e9
-bp["p2p"] = []
-for tiles in (1,):
-    for panels in (4,):
-        os.environ["B2MM_TILES_PER_CLUSTER"] = str(tiles)
-        t = timed(lambda: comm.bmm_allreduce_p2p(A3, B3, sharedC, panels))
-        bp["p2p"].append({"tiles_per_cluster": tiles, "panels": panels, "ms": t})
-bestp = min(bp["p2p"], key=lambda r: r["ms"])
-os.environ["B2MM_TILES_PER_CLUSTER"] = str(bestp["tiles_per_cluster"])
-prounds = []
-for _ in range(1):
-    tg = timed(lambda: b2.bmm(A3, B3, out=C3), iters=8, warm=1)
-    to = timed(lambda: comm.bmm_allreduce_p2p(A3, B3, sharedC, bestp["panels"]), iters=8, warm=1)
-    prounds.append({"gemm_only_ms": tg, "p2p_ms": to, "weak_eff": tg / to})
-bp["gemm_per_iter"] = timed_each(lambda: b2.bmm(A3, B3, out=C3))
-bp["nccl_overlap_per_iter"] = timed_each(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, best["panels"]))
-bp["p2p_best"] = bestp
-bp["p2p_interleaved_rounds"] = prounds
-bp["p2p_weak_scaling_eff"] = sum(r["weak_eff"] for r in prounds) / len(prounds)
-# parity of the p2p pipeline against NCCL's all_reduce of the same product
-comm.bmm_allreduce_p2p(A3, B3, sharedC, 4)
+rounds = []
+for _ in range(3):
+    tg = timed(lambda: b2.bmm(A3, B3, out=C3), iters=6, warm=2)
+    tn = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, 8), iters=6, warm=2)
+    tg2 = timed(lambda: b2.bmm(A3, B3, out=C3), iters=6, warm=2)
+    tf = timed(lambda: comm.bmm_allreduce_fused(A3, B3, sharedC, 8), iters=6, warm=2)
+    rounds.append({"gemm_only_ms": tg, "nccl_pipelined_ms": tn, "nccl_eff": tg / tn,
+                   "gemm_only_again_ms": tg2, "fused_ms": tf, "fused_eff": tg2 / tf})
+bp["interleaved_rounds"] = rounds
+bp["nccl_pipelined_weak_eff"] = sum(r["nccl_eff"] for r in rounds) / len(rounds)
+bp["fused_weak_eff"] = sum(r["fused_eff"] for r in rounds) / len(rounds)
+# parity of the fused path against NCCL's all_reduce of the same product
+comm.bmm_allreduce_fused(A3, B3, sharedC, 8)
 b2.bmm(A3, B3, out=C3)
 comm.all_reduce(C3)
 torch.cuda.synchronize()
 ref = C3[0, :256].double()
-bp["p2p_vs_nccl_err"] = max_ranks(((sharedC.local[0, :256].double() - ref).abs() / (ref.abs() + ref.pow(2).mean().sqrt())).max().item())
-bp["best"] = best
-bp["interleaved_rounds"] = rounds
-bp["weak_scaling_eff"] = sum(r["weak_eff"] for r in rounds) / len(rounds)
+bp["fused_vs_nccl_err"] = max_ranks(((sharedC.local[0, :256].double() - ref).abs() / (ref.abs() + ref.pow(2).mean().sqrt())).max().item())
 res["batch_parallel_weak_b1"] = bp
 
 # ---- matrix_parallel ----

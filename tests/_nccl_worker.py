@@ -1,0 +1,110 @@
+"""Worker for test_collectives_gpu.py: the library's collectives and fused paths on >= 2 GPUs (one process per GPU).
+
+Every result is checked on every rank against values computed independently: the oracle (exact products, double
+sum) for GEMM content, and plain float64 sums of the per-rank inputs for the reductions."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from oracle import oracle, reference_port  # noqa: E402
+import pytorch_distributed_matmul_benchmark_b200 as b2  # noqa: E402
+from pytorch_distributed_matmul_benchmark_b200 import _lib, hostlib  # noqa: E402
+
+TOL = {torch.bfloat16: 4e-3, torch.float16: 5e-4, torch.float32: 2e-5}
+
+
+def rel(C, ref):
+    ref = ref.double().cpu()
+    rms = ref.pow(2).mean().sqrt()
+    return ((C.double().cpu() - ref).abs() / (ref.abs() + rms)).max().item()
+
+
+def main(out_path):
+    rank, ws = hostlib.setup_distributed()
+    dev = hostlib.rank_device(rank)
+    comm = b2.Communicator(rank, ws, torch.device(dev))
+    res = {}
+
+    # all_reduce / all_gather through NCCL owned by the library
+    for dt in (torch.bfloat16, torch.float32):
+        torch.manual_seed(100 + rank)
+        x = torch.randn(3, 1000, dtype=dt, device=dev)
+        want = sum(torch.randn(3, 1000, dtype=dt, generator=torch.Generator().manual_seed(0)) * 0 for _ in range(1))  # placeholder shape
+        parts = []
+        for r in range(ws):
+            torch.manual_seed(100 + r)
+            parts.append(torch.randn(3, 1000, dtype=dt, device=dev).double())
+        want = sum(parts)
+        torch.manual_seed(100 + rank)
+        x = torch.randn(3, 1000, dtype=dt, device=dev)
+        comm.all_reduce(x)
+        torch.cuda.synchronize()
+        res[f"all_reduce_{dt}"] = rel(x, want) <= (ws - 1) * TOL[dt] + 1e-6
+        slabs = torch.zeros(ws, 3, 1000, dtype=dt, device=dev)
+        torch.manual_seed(100 + rank)
+        mine = torch.randn(3, 1000, dtype=dt, device=dev)
+        comm.all_gather_into(slabs, mine)
+        torch.cuda.synchronize()
+        res[f"all_gather_{dt}"] = all(torch.equal(slabs[r].double(), parts[r]) for r in range(ws))
+        # own peer-memory all_reduce: fp32 adds, one rounding
+        sh = comm.shared_like(mine)
+        sh.local.copy_(mine)
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.all_reduce_p2p(sh)
+        torch.cuda.synchronize()
+        res[f"all_reduce_p2p_{dt}"] = rel(sh.local, want) <= TOL[dt]
+    comm.all_reduce(torch.empty(0, dtype=torch.bfloat16, device=dev))  # local batch 0 (ws = 8 in the reference): no-op
+    res["empty_all_reduce"] = True
+
+    # matrix_parallel, fused GEMM + all_gather: every rank ends up with the global product
+    N = 1024
+    A, Bfull, B_local, (s, e) = reference_port.matrix_parallel_inputs(rank, ws, N, torch.bfloat16, device=dev)
+    shared = comm.shared_slabs(N, e - s, torch.bfloat16)
+    shared.local.zero_()
+    torch.cuda.synchronize()
+    dist.barrier()
+    for _ in range(2):
+        comm.matmul_allgather_fused(A, B_local, shared)
+    torch.cuda.synchronize()
+    Cg = torch.cat(list(shared.local.unbind(0)), dim=1)
+    res["fused_allgather"] = rel(Cg, oracle.gemm_block_f64(A.cpu(), Bfull.cpu(), 0, N, 0, N)) <= TOL[torch.bfloat16]
+    slabs = torch.zeros(ws, N, e - s, dtype=torch.bfloat16, device=dev)
+    C_local = b2.matmul(A, B_local)
+    comm.all_gather_into(slabs, C_local)
+    torch.cuda.synchronize()
+    res["fused_allgather_equals_nccl_path"] = torch.equal(slabs, shared.local)
+
+    # batch_parallel, fused GEMM + all_reduce: sum over ranks of the per-rank products
+    Ab, Bb = reference_port.batch_parallel_inputs(rank, ws, 1024, torch.bfloat16, batch_size=2 * ws, device=dev)
+    shC = comm.shared_like(torch.empty(2, 1024, 1024, dtype=torch.bfloat16, device=dev))
+    for _ in range(2):
+        comm.bmm_allreduce_fused(Ab, Bb, shC, 2)
+    torch.cuda.synchronize()
+    want = 0
+    for r in range(ws):
+        Ar, Br = reference_port.batch_parallel_inputs(r, ws, 1024, torch.bfloat16, batch_size=2 * ws, device=dev)
+        want = want + b2.bmm(Ar, Br).double()  # each rank's bf16 C, as the reference reduces rounded C tensors
+    res["fused_allreduce"] = rel(shC.local, want) <= TOL[torch.bfloat16]
+    Cn = b2.bmm(Ab, Bb)
+    comm.all_reduce(Cn)
+    torch.cuda.synchronize()
+    res["fused_allreduce_vs_nccl"] = rel(shC.local, Cn.double()) <= (ws - 1) * TOL[torch.bfloat16]
+    res["launches"] = _lib.launch_count()
+
+    comm.destroy()
+    hostlib.cleanup_distributed()
+    if rank == 0:
+        json.dump(res, open(out_path, "w"))
+    else:
+        json.dump(res, open(out_path + f".rank{rank}", "w"))
+
+
+if __name__ == "__main__":
+    main(sys.argv[1])

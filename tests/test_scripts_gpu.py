@@ -60,4 +60,5 @@ def test_scaling_script_two_gpus(mode, extra):
     if "--overlap" in extra:
         assert "Overlapped end-to-end:" in out
     if "--fused" in extra:
-        assert "Fused GEMM+all_" in out and out.count("-> OK") >= 2
+        assert "Fused GEMM+all_" in out
+        assert out.count("-> OK") >= (2 if mode == "batch_parallel" else 1)  # local bmm parity + fused-vs-NCCL parity

@@ -211,6 +211,16 @@ B2MM_API int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void*
 B2MM_API int b2mm_all_reduce_p2p(void* comm, void* const* peer_bufs, int64_t count, int dtype, b2mm_stream_t stream);
 
 /*
+ * The same reduction with its cross-GPU synchronisation inside the kernels (epoch counters in the
+ * peer-mapped signal pads, see b2mm_gemm_allreduce_fused) instead of NCCL barriers, and built to be
+ * co-resident with a GEMM running on another stream: this is what overlaps dist.all_reduce(C) with the
+ * next matmul in the double-buffered and pipelined modes of backup/matmul_overlap_benchmark.py:93-278.
+ * Complete, on `stream`, when every rank's result has landed in every buffer.
+ */
+B2MM_API int b2mm_all_reduce_p2p_sync(void* comm, void* const* peer_bufs, void* const* peer_signals, int64_t count,
+                                      int dtype, b2mm_stream_t stream);
+
+/*
  * batch_parallel as a pipeline of this library's own kernels (matmul_scaling_benchmark.py:142 + :150):
  * C = bmm(A, B) in row panels on `compute`, written into peer_C[rank]; behind each panel, on
  * `comm_stream`: barrier, then the peer-memory all-reduce of that panel (as b2mm_all_reduce_p2p).

@@ -362,6 +362,74 @@ int b2mm_gemm_allreduce_p2p(void* comm, const void* A, const void* B, void* cons
   return B2MM_OK;
 }
 
+// CTAs of two kernels share an SM only if both ask for the same L1/shared-memory split: the GEMM runs with
+// the maximum shared-memory carve-out, so the (shared-memory-free) reduction kernels ask for it too.
+static constexpr int kSyncUnroll = 4;
+static void prefer_gemm_carveout() {
+  static std::once_flag once[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return;
+  std::call_once(once[dev], [] {
+    const int co = cudaSharedmemCarveoutMaxShared;
+    cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__nv_bfloat16, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__half, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    cudaFuncSetAttribute(allreduce_p2p_sync_kernel<float, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    cudaFuncSetAttribute(p2p_done_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+  });
+}
+
+// One self-synchronising reduction launch (see allreduce_p2p.cuh) over this rank's slice of
+// [elem_off, elem_off + count); band_counter may be null.
+static int launch_sync_reduce(Comm* c, const PeerPtrs& pp, const SignalPtrs& sp, int64_t elem_off, int64_t count, int dtype,
+                              const int* band_counter, int band_target, cudaStream_t cs) {
+  const int es = dtype_bytes(dtype);
+  const int64_t vecs = count * es / 16, per = vecs / c->world;
+  const int64_t begin = elem_off * es / 16 + per * c->rank;
+  const int64_t mine = (c->rank == c->world - 1) ? vecs - per * (c->world - 1) : per;
+  // Fewer CTAs than SMs on purpose: should these CTAs ever fail to share SMs with a GEMM's, the GEMM still
+  // finds free SMs and the device-side waits end (slowly) instead of deadlocking.
+  const char* v = getenv("B2MM_P2P_CTAS");
+  int ctas = (v && *v) ? atoi(v) : device_sm_count() - 8;
+  if (ctas < 1) ctas = 1;
+  const int epoch = ++c->ready_epoch;
+  switch (dtype) {
+    case B2MM_BF16: allreduce_p2p_sync_kernel<__nv_bfloat16, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
+    case B2MM_FP16: allreduce_p2p_sync_kernel<__half, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
+    default: allreduce_p2p_sync_kernel<float, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "peer all_reduce launch failed: %s", cudaGetErrorString(e));
+  count_launch(1);
+  return B2MM_OK;
+}
+
+static int launch_done(Comm* c, const SignalPtrs& sp, cudaStream_t cs) {
+  p2p_done_kernel<<<1, 32, 0, cs>>>(sp, c->rank, c->world, ++c->done_epoch);
+  if (cudaGetLastError() != cudaSuccess) return fail(B2MM_ERR_CUDA, "done-signal launch failed");
+  count_launch(1);
+  return B2MM_OK;
+}
+
+int b2mm_all_reduce_p2p_sync(void* comm, void* const* peer_bufs, void* const* peer_signals, int64_t count, int dtype,
+                             b2mm_stream_t stream) {
+  Comm* c = (Comm*)comm;
+  if (!c || !peer_bufs || !peer_signals || count < 0 || !dtype_bytes(dtype) || c->world > 8)
+    return fail(B2MM_ERR_BAD_ARG, "bad p2p all_reduce argument");
+  if (count == 0) return B2MM_OK;
+  if ((count * dtype_bytes(dtype)) % 16) return fail(B2MM_ERR_UNSUPPORTED, "p2p all_reduce needs a multiple of 16 bytes");
+  PeerPtrs pp;
+  SignalPtrs sp;
+  for (int d = 0; d < 8; ++d) {
+    pp.p[d] = peer_bufs[d < c->world ? d : 0];
+    sp.p[d] = (int*)peer_signals[d < c->world ? d : 0];
+  }
+  prefer_gemm_carveout();
+  int rc;
+  if ((rc = launch_sync_reduce(c, pp, sp, 0, count, dtype, nullptr, 0, (cudaStream_t)stream))) return rc;
+  return launch_done(c, sp, (cudaStream_t)stream);
+}
+
 int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* const* peer_C, void* const* peer_signals,
                               int* band_counters, int64_t N, int64_t local_batch, int dtype, int n_bands, void* workspace,
                               size_t workspace_bytes, b2mm_stream_t compute_, b2mm_stream_t comm_stream_) {
@@ -382,27 +450,7 @@ int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* co
     pp.p[d] = peer_C[d < c->world ? d : 0];
     sp.p[d] = (int*)peer_signals[d < c->world ? d : 0];
   }
-  // Fewer CTAs than SMs on purpose: should the reduction's CTAs ever fail to share SMs with the GEMM's, the
-  // GEMM still finds free SMs and the wait below ends (slowly) instead of deadlocking.
-  const char* v = getenv("B2MM_P2P_CTAS");
-  int ctas = (v && *v) ? atoi(v) : device_sm_count() - 8;
-  if (ctas < 1) ctas = 1;
-  constexpr int kUnroll = 4;
-  {
-    // CTAs of two kernels share an SM only if both ask for the same L1/shared-memory split: the GEMM runs
-    // with the maximum shared-memory carve-out, so the (shared-memory-free) reduction asks for it too.
-    static std::once_flag once[64];
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64)
-      std::call_once(once[dev], [] {
-        const int co = cudaSharedmemCarveoutMaxShared;
-        cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__nv_bfloat16, kUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-        cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__half, kUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-        cudaFuncSetAttribute(allreduce_p2p_sync_kernel<float, kUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-        cudaFuncSetAttribute(p2p_done_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-      });
-  }
+  prefer_gemm_carveout();
   // compute: clear the progress counters, then ONE GEMM over the whole batch on the whole device; its
   // epilogues count finished tiles per row band.
   const int total_bands = (int)(n_bands * local_batch);
@@ -420,23 +468,12 @@ int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* co
   for (int64_t b = 0; b < local_batch; ++b) {
     for (int i = 0; i < n_bands; ++i) {
       const int64_t elem_off = b * N * N + (int64_t)i * band_rows * N;
-      const int64_t vecs = band_rows * N * es / 16, per = vecs / c->world;
-      const int64_t begin = elem_off * es / 16 + per * c->rank;
-      const int epoch = ++c->ready_epoch;
-      const int* ctr = band_counters + b * n_bands + i;
-      switch (dtype) {
-        case B2MM_BF16: allreduce_p2p_sync_kernel<__nv_bfloat16, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per, ctr, opts.signals_per_band); break;
-        case B2MM_FP16: allreduce_p2p_sync_kernel<__half, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per, ctr, opts.signals_per_band); break;
-        default: allreduce_p2p_sync_kernel<float, kUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, per, ctr, opts.signals_per_band); break;
-      }
-      cudaError_t e = cudaGetLastError();
-      if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "fused all_reduce launch failed: %s", cudaGetErrorString(e));
-      count_launch(1);
+      if ((rc = launch_sync_reduce(c, pp, sp, elem_off, band_rows * N, dtype, band_counters + b * n_bands + i,
+                                   opts.signals_per_band, cs)))
+        return rc;
     }
   }
-  p2p_done_kernel<<<1, 32, 0, cs>>>(sp, c->rank, c->world, ++c->done_epoch);
-  if (cudaGetLastError() != cudaSuccess) return fail(B2MM_ERR_CUDA, "done-signal launch failed");
-  count_launch(1);
+  if ((rc = launch_done(c, sp, cs))) return rc;
   if (cudaEventRecord(c->comm_done, cs) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
   if (cudaStreamWaitEvent(compute, c->comm_done, 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
   return B2MM_OK;

@@ -99,6 +99,7 @@ class Ops:
     matmul_allgather_fused: Optional[Callable] = None  # (A, B_local, shared) -> slabs
     shared_like: Optional[Callable] = None  # (t) -> SharedSlabs
     bmm_allreduce_fused: Optional[Callable] = None  # (A, B, shared_C, n_panels) -> C
+    all_reduce_sync: Optional[Callable] = None  # (shared, stream=None) -> t; peer-memory all_reduce, co-resident with a GEMM
     synchronize: Callable = torch.cuda.synchronize
     event: Callable = lambda: torch.cuda.Event(enable_timing=True)
     destroy: Callable = lambda: None
@@ -123,6 +124,7 @@ def device_ops(rank: int, world_size: int, device: str) -> Ops:
         matmul_allgather_fused=comm.matmul_allgather_fused if comm else None,
         shared_like=comm.shared_like if comm else None,
         bmm_allreduce_fused=comm.bmm_allreduce_fused if comm else None,
+        all_reduce_sync=comm.all_reduce_sync if comm else None,
         destroy=comm.destroy if comm else (lambda: None),
     )
 

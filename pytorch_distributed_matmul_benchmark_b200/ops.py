@@ -295,15 +295,26 @@ class Communicator:
             ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(), self.comm_stream.cuda_stream))
         return shared_C.local
 
-    def bmm_allreduce_fused(self, A: torch.Tensor, B: torch.Tensor, shared_C: "SharedSlabs", n_panels: int = 4) -> torch.Tensor:
-        """C = bmm(A, B) in row panels; each panel summed over ranks by a self-synchronising peer-memory kernel
-        that shares the SMs with the next panel's GEMM (no NCCL, nothing reserved)."""
-        _require_cuda(A, B)
+    def _signal_pads(self) -> "SharedSlabs":
         if getattr(self, "_signals", None) is None:
             pad = torch.zeros(64, dtype=torch.int32, device=self.device)
             torch.cuda.synchronize(self.device)
             self._signals = self.share(pad)
             self._band_counters = torch.zeros(256, dtype=torch.int32, device=self.device)
+        return self._signals
+
+    def all_reduce_sync(self, shared: "SharedSlabs", stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """In-place SUM over ranks by the self-synchronising peer-memory kernels (no NCCL); may run beside a GEMM."""
+        t = shared.local
+        _lib.check(_lib.load().b2mm_all_reduce_p2p_sync(self._comm, shared.peer_ptrs, self._signal_pads().peer_ptrs, t.numel(),
+                                                        _dtype_code(t), _stream_ptr(stream)))
+        return t
+
+    def bmm_allreduce_fused(self, A: torch.Tensor, B: torch.Tensor, shared_C: "SharedSlabs", n_panels: int = 4) -> torch.Tensor:
+        """C = bmm(A, B) in row panels; each panel summed over ranks by a self-synchronising peer-memory kernel
+        that shares the SMs with the next panel's GEMM (no NCCL, nothing reserved)."""
+        _require_cuda(A, B)
+        self._signal_pads()
         b, N, _ = A.shape
         code = _dtype_code(A)
         ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)

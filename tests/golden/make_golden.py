@@ -37,6 +37,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REF)
 import matmul_benchmark as mb  # noqa: E402
 import matmul_scaling_benchmark as ms  # noqa: E402
+sys.path.insert(0, os.path.join(REF, "backup"))
+import matmul_overlap_benchmark as ov  # noqa: E402
 
 DT = {"float32": torch.float32, "float16": torch.float16, "bfloat16": torch.bfloat16}
 
@@ -181,6 +183,19 @@ def gen_host_logic():
     finally:
         ms.benchmark_independent, ms.benchmark_batch_parallel, ms.benchmark_matrix_parallel = saved
     out["fake_time"] = fake_time
+
+    # backup/matmul_overlap_benchmark.py: CLI and report text (its three modes are first-class here)
+    out["cli_ov_default"] = cli(ov, [])  # rank, world, sizes, dtype, mode, iters, warmup
+    out["modes_ov"] = [m.value for m in ov.BenchmarkMode]
+    saved = (ov.benchmark_no_overlap, ov.benchmark_overlap, ov.benchmark_pipeline)
+    stub = lambda size, dtype, device, rank, it, wu: (fake_time, ov.calculate_tflops(size, fake_time), 0.0)  # noqa: E731
+    ov.benchmark_no_overlap = ov.benchmark_overlap = ov.benchmark_pipeline = stub
+    try:
+        for mode in ov.BenchmarkMode:
+            out[f"report_ov_{mode.value}"] = capture_report(
+                ov, lambda mode=mode: ov.run_benchmarks(0, 1, [4096, 16384], torch.bfloat16, mode, 50, 10))
+    finally:
+        ov.benchmark_no_overlap, ov.benchmark_overlap, ov.benchmark_pipeline = saved
 
     # The reference's own CPU path, executed here once as a record (config 1 of BASELINE.json, reduced iterations)
     with contextlib.redirect_stdout(io.StringIO()):

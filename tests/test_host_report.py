@@ -118,3 +118,31 @@ def test_launchers_keep_the_reference_positionals():
 def test_cpu_device_is_refused_by_the_product_benchmark():
     with pytest.raises(RuntimeError, match="no CPU path"):
         mb.benchmark_matmul(64, torch.float32, "cpu", 1, 0)
+
+
+# ---- backup/matmul_overlap_benchmark.py: its three modes are first-class here ----------------------------
+from pytorch_distributed_matmul_benchmark_b200 import matmul_overlap_benchmark as ov  # noqa: E402
+
+
+def test_overlap_cli_defaults_match_reference(host_logic):
+    a = ov.build_parser().parse_args([])
+    assert [0, 1, a.sizes, str(hostlib.DTYPE_MAP[a.dtype]), a.mode, a.iterations, a.warmup] == host_logic["cli_ov_default"]
+    assert [m.value for m in ov.BenchmarkMode] == host_logic["modes_ov"]
+    assert ov.PIPELINE_DEPTH == 3  # backup/matmul_overlap_benchmark.py:184
+    with pytest.raises(SystemExit):
+        ov.build_parser().parse_args(["--mode", "independent"])
+
+
+@pytest.mark.parametrize("mode", list(ov.BenchmarkMode))
+def test_overlap_report_text_matches_reference(host_logic, mode):
+    t = host_logic["fake_time"]
+    stubs = {m: (lambda size: (t, hostlib.calculate_tflops(size, t), 0.0)) for m in ov.BenchmarkMode}
+    out = _capture(lambda: ov.run_benchmarks(0, 1, [4096, 16384], torch.bfloat16, mode, 50, 10, bench_fns=stubs, device="cpu"))
+    assert out == host_logic[f"report_ov_{mode.value}"]
+
+
+def test_overlap_launcher_keeps_the_reference_positionals():
+    text = open(os.path.join(ROOT, "run_overlap_benchmark.sh")).read()
+    assert "NUM_GPUS=${1:-2}" in text and "MODE=${2:-overlap}" in text and "DTYPE=${3:-bfloat16}" in text
+    assert "--master_port=29502" in text and "--sizes 4096 8192 16384 --iterations 50 --warmup 10" in text
+    subprocess.check_call(["bash", "-n", os.path.join(ROOT, "run_overlap_benchmark.sh")])

@@ -62,3 +62,22 @@ def test_scaling_script_two_gpus(mode, extra):
     if "--fused" in extra:
         assert "Fused GEMM+all_" in out
         assert out.count("-> OK") >= (2 if mode == "batch_parallel" else 1)  # local bmm parity + fused-vs-NCCL parity
+
+
+@pytest.mark.parametrize("mode", ["no_overlap", "overlap", "pipeline"])
+def test_overlap_script_single_gpu(mode):
+    out = _run([sys.executable, "matmul_overlap_benchmark.py", "--sizes", "1024", "--iterations", "4", "--warmup", "2",
+                "--mode", mode])
+    assert f"  - Mode: {mode}" in out and "Results for 1024x1024:" in out and "ERROR" not in out
+    assert re.search(r"  - Actual TFLOPS: \d+\.\d\d \(FLOPs/Time\)", out)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("mode", ["no_overlap", "overlap", "pipeline"])
+def test_overlap_script_two_gpus(mode):
+    out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                "--master-addr=127.0.0.1", f"--master-port={_free_port()}", "matmul_overlap_benchmark.py", "--sizes",
+                "2048", "--iterations", "5", "--warmup", "2", "--mode", mode, "--check"])
+    assert "Results for 2048x2048:" in out and "ERROR" not in out and "FAIL" not in out
+    assert "Parity of the reduced product" in out and "-> OK" in out
+    assert "  - Note: In data parallel, each GPU does full matrix multiply" in out

@@ -61,8 +61,32 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 3-D map over a (batch, rows, cols) row-major array: dims {cols, rows, batch}.
+// Encoding costs ~1 us on the host and a benchmark calls with the same buffers over and over, so the
+// last few maps are kept per thread, keyed by everything that goes into them.
+struct MapKey {
+  const void* ptr;
+  int64_t cols, rows, batch, ld, batch_stride;
+  int dtype;
+  uint32_t box_cols, box_rows;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && cols == o.cols && rows == o.rows && batch == o.batch && ld == o.ld &&
+           batch_stride == o.batch_stride && dtype == o.dtype && box_cols == o.box_cols && box_rows == o.box_rows;
+  }
+};
+static constexpr int kMapCache = 32;
+static thread_local MapKey t_map_keys[kMapCache];
+static thread_local CUtensorMap t_map_vals[kMapCache];
+static thread_local int t_map_used = 0, t_map_next = 0;
+
 static int make_map(CUtensorMap* map, const void* ptr, int dtype, int64_t cols, int64_t rows, int64_t batch,
                     int64_t ld, int64_t batch_stride, uint32_t box_cols, uint32_t box_rows) {
+  if (batch <= 1) batch_stride = rows * ld;
+  const MapKey key{ptr, cols, rows, batch, ld, batch_stride, dtype, box_cols, box_rows};
+  for (int i = 0; i < t_map_used; ++i)
+    if (t_map_keys[i] == key) {
+      *map = t_map_vals[i];
+      return B2MM_OK;
+    }
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return fail(B2MM_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   const int es = dtype_bytes(dtype);
@@ -70,7 +94,6 @@ static int make_map(CUtensorMap* map, const void* ptr, int dtype, int64_t cols, 
                            : dtype == B2MM_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
                                                 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)(batch > 0 ? batch : 1)};
-  if (batch <= 1) batch_stride = rows * ld;
   cuuint64_t strides[2] = {(cuuint64_t)ld * es, (cuuint64_t)batch_stride * es};
   cuuint32_t box[3] = {box_cols, box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
@@ -79,6 +102,9 @@ static int make_map(CUtensorMap* map, const void* ptr, int dtype, int64_t cols, 
   if (r != CUDA_SUCCESS)
     return fail(B2MM_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d): cols=%lld rows=%lld batch=%lld ld=%lld", (int)r,
                 (long long)cols, (long long)rows, (long long)batch, (long long)ld);
+  const int slot = t_map_used < kMapCache ? t_map_used++ : (t_map_next++ % kMapCache);
+  t_map_keys[slot] = key;
+  t_map_vals[slot] = *map;
   return B2MM_OK;
 }
 

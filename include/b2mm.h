@@ -64,11 +64,10 @@ B2MM_API const char* b2mm_last_error(void);
  * (all threads).  bench.py reports the delta over its timed region. */
 B2MM_API uint64_t b2mm_launch_count(void);
 
-/* Tools only (scripts/trace_tiles.py): when non-null, every GEMM launched afterwards
- * writes into this device buffer of (1 + ceil(tiles / clusters)) * grid uint64
- * entries: row 0 = the SM id of each CTA, row 1 + i = the global-timer value at
- * which the CTA's producer started its i-th tile.  Pass NULL to switch it off.
- * No counterpart in the reference. */
+/* Tools only (scripts/trace_tiles.py): when non-null, every GEMM launched afterwards writes into this
+ * device buffer, laid out as rows of 256 uint64 indexed by SM id: row 0 = 1 + the first tile index of the
+ * CTA on that SM, row 1 + i = the global-timer value at which its producer started its i-th tile
+ * (at least 2 + tiles / 74 rows).  Pass NULL to switch it off.  No counterpart in the reference. */
 B2MM_API void b2mm_debug_set_trace(void* device_buffer);
 
 /*

@@ -6,21 +6,24 @@
 // call sites (matmul_benchmark.py:62, matmul_scaling_benchmark.py:92,142,211).
 //
 // Data movement and layout
-//   A is the K-major UMMA operand: TMA box {BLOCK_K, 128 rows}, 128B swizzle.
+//   A is the K-major UMMA operand: TMA box {BLOCK_K, CTA_M rows}, 128B swizzle.
 //   B is row-major K x N, i.e. the MN-major UMMA operand: TMA boxes of
 //   {N_ATOM columns (128 bytes), BLOCK_K rows}, 128B swizzle; the tensor core
 //   transposes on read, so B is never transposed in memory.
 //   Both land in a kStages-deep shared-memory ring guarded by full/empty
 //   mbarriers.  With kCtaGroup == 2 a CTA pair (one cluster) works on one
-//   (256 x BLOCK_N) tile: each CTA loads its own 128 rows of A and HALF of the
-//   B columns; tcgen05.mma.cta_group::2 reads both halves.
+//   (2 * CTA_M) x BLOCK_N tile: each CTA loads its own CTA_M rows of A and HALF
+//   of the B columns; tcgen05.mma.cta_group::2 (M = 256) reads both halves.
 //
-// Tile shapes.  kMBlocks == 2 (the default for 16-bit inputs) gives each CTA a
-// 256-row slab: per k-block it loads 32 KB of A and 16 KB of B for 2 x 4 MMAs,
-// 48 B/cycle/SM from L2 instead of the 64 B/cycle/SM of the 128-row slab.  That
-// matters twice on B200: the part is power limited, and at 64 B/cycle/SM some
-// TPCs are L2-bandwidth starved (measured: two SM populations 4 % apart), which
-// lets clusters drift apart in k and destroys their sharing of panels in L2.
+// Tile shapes and TMEM.  Accumulators live in TMEM (512 fp32 columns per CTA).
+//   kMBlocks == 1: CTA_M = 128, two BLOCK_N-column accumulators, double buffered: the epilogue
+//   of tile i overlaps the main loop of tile i+1.
+//   kMBlocks == 2 (the default for 16-bit inputs when the problem fills the machine): CTA_M = 256,
+//   the two 128-row halves X and Y of the tile fill TMEM.  Per k-block a CTA loads 32 KB of A and
+//   16 KB of B for 2 x 4 MMAs: 48 B/cycle/SM from L2 instead of 64, a quarter less L2->SM traffic
+//   per flop on a part whose clock is set by its power cap.  TMEM is then single buffered, so the
+//   MMA warp gets a kStagger-k-block head start on X of the next tile while the epilogue is still
+//   draining Y.
 //
 // Warp roles (224 threads)
 //   warp 0      TMA producer (one elected lane)
@@ -29,15 +32,13 @@
 //   warp 6      tile scheduler (one elected lane, leader CTA only; dynamic mode)
 //
 // Tile scheduling.  Static: grid = min(#SM, tiles) CTAs, cluster c takes tiles c, c + C, ...
-// (used when the caller caps the SMs, i.e. when a collective runs beside the GEMM).
-// Dynamic (default): the grid has one cluster per tile; the clusters that get to run keep
-// their TMEM/barriers/pipeline and ask the hardware for the next not-yet-launched cluster's
-// index (clusterlaunchcontrol.try_cancel), so faster SMs simply process more tiles and the
-// tiles in flight stay adjacent in raster order (measured on B200: per-SM tile times differ
-// by up to 5 % by TPC position, which makes a static split finish at the pace of the slowest).
-//
-// Accumulators live in TMEM, double buffered (2 x BLOCK_N fp32 columns), so
-// the epilogue of tile i overlaps the main loop of tile i+1.
+// (used when the caller caps the SMs).  Dynamic (default): the grid has one cluster per tile;
+// the clusters that get to run keep their TMEM/barriers/pipeline and ask the hardware for the
+// next not-yet-launched cluster's index (clusterlaunchcontrol.try_cancel), so faster SMs simply
+// process more tiles and the tiles in flight stay adjacent in raster order.  Measured on B200:
+// per-SM tile times differ by up to 5 % with a fixed pattern over TPC position (whatever the
+// L2 demand), so a static split finishes at the pace of the slowest SM and its clusters drift
+// apart in k, which destroys their sharing of A/B panels in L2.
 //
 // kSplit == 2 is the fp32 path (3xTF32): A and B^T each arrive as a (hi, lo)
 // pair of TF32-exact fp32 arrays (written by the split kernels at the end of
@@ -76,8 +77,9 @@ struct GemmParams {
   int* band_counter;
   int band_tiles;       // tile rows per band
   int bands_per_batch;
-  // Optional trace buffer (tools only; null in production): per CTA, per tile
-  // iteration, the global-timer value at which the producer started the tile.
+  // Optional trace buffer (tools only; null in production), rows of 256 uint64 indexed by SM id:
+  // row 0 = 1 + first tile index, row 1 + i = global-timer value at which the producer started
+  // this CTA's i-th tile.
   unsigned long long* trace;
 };
 

@@ -191,6 +191,7 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   p.hint_a = kHints[env_int("B2MM_HINT_A", 0) % 3];
   p.hint_b = kHints[env_int("B2MM_HINT_B", 0) % 3];
   p.trace = g_trace;
+  p.debug_same_k = g_trace ? env_int("B2MM_DEBUG_SAMEK", 0) : 0;  // only together with the trace tool
   p.fanout = o.fanout;
   p.max_tiles = o.tiles_per_cluster;
   p.band_counter = o.band_counter;

@@ -81,6 +81,7 @@ struct GemmParams {
   // row 0 = 1 + first tile index, row 1 + i = global-timer value at which the producer started
   // this CTA's i-th tile.
   unsigned long long* trace;
+  int debug_same_k;  // tools only: every k-block loads k = 0 (all L2 hits; results are meaningless)
 };
 
 enum class InKind : int { BF16 = 0, FP16 = 1, TF32 = 2 };
@@ -340,7 +341,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (cta_rank == 0) mbar_arrive_expect_tx(fb_local, (uint32_t)(G * Cfg::STAGE_BYTES));
           const uint32_t sA = tiles + stage * Cfg::STAGE_BYTES;
           const uint32_t sB = sA + Cfg::kSplit * Cfg::A_BYTES;
-          const int k0 = kb * Cfg::BLOCK_K;
+          const int k0 = p.debug_same_k ? 0 : kb * Cfg::BLOCK_K;
           tma_load_3d<G>(sA, &tmA, fb, k0, m_row, b, p.hint_a);
           if constexpr (Cfg::kSplit == 2) tma_load_3d<G>(sA + Cfg::A_BYTES, &tmA_lo, fb, k0, m_row, b, p.hint_a);
           if constexpr (Cfg::kBKMajor) {

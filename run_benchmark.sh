@@ -1,23 +1,9 @@
 #!/bin/bash
-# Same positional interface as the reference launcher: NUM_GPUS [DTYPE].
-# Anything after the two positionals is passed through (e.g. --check, --json out.json).
-
+# Drop-in for the reference launcher of the same name: run_benchmark.sh [NUM_GPUS=1] [DTYPE=bfloat16] [extra flags...]
+# (extra flags, e.g. --check or --json out.json, go to matmul_benchmark.py unchanged).
+source "$(dirname "$0")/run_common.sh"
 NUM_GPUS=${1:-1}
 DTYPE=${2:-bfloat16}
 shift $(( $# < 2 ? $# : 2 ))
-cd "$(dirname "$0")"
-
-echo "Starting distributed matrix multiplication benchmark with $NUM_GPUS GPU(s)"
-echo "Data type: $DTYPE"
-echo ""
-
-ARGS="--sizes 4096 8192 16384 --iterations 50 --warmup 10 --dtype $DTYPE"
-if [ "$NUM_GPUS" -eq 1 ]; then
-    echo "Running in single GPU mode..."
-    python3 matmul_benchmark.py $ARGS "$@"
-else
-    echo "Running in distributed mode with $NUM_GPUS GPUs..."
-    python3 -m torch.distributed.run --nnodes=1 --nproc_per_node=$NUM_GPUS \
-        --master_addr=127.0.0.1 --master_port=29500 \
-        matmul_benchmark.py $ARGS "$@"
-fi
+printf 'Starting distributed matrix multiplication benchmark with %s GPU(s)\nData type: %s\n\n' "$NUM_GPUS" "$DTYPE"
+b2mm_launch "$NUM_GPUS" 29500 matmul_benchmark.py "${B2MM_DEFAULT_SWEEP[@]}" --dtype "$DTYPE" "$@"

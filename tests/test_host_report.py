@@ -101,17 +101,35 @@ def test_calculate_tflops_and_split_match_reference(host_logic):
         assert hostlib.split_columns(N, ws, rank) == (s, e)
 
 
+def _dry_run(script, *args):
+    """Run a launcher with python3 / torchrun replaced by an echo stub; returns what it would have executed."""
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        stub = os.path.join(d, "python3")
+        open(stub, "w").write("#!/bin/bash\necho CMD: python3 \"$@\"\n")
+        os.chmod(stub, 0o755)
+        env = dict(os.environ, PATH=d + os.pathsep + os.environ["PATH"])
+        return subprocess.run(["bash", os.path.join(ROOT, script), *args], env=env, capture_output=True, text=True, check=True).stdout
+
+
 def test_launchers_keep_the_reference_positionals():
-    """run_benchmark.sh: NUM_GPUS [DTYPE]; run_scaling_benchmark.sh: NUM_GPUS [MODE] [DTYPE] (defaults 1/bf16, 2/independent/bf16)."""
-    rb = open(os.path.join(ROOT, "run_benchmark.sh")).read()
-    rs = open(os.path.join(ROOT, "run_scaling_benchmark.sh")).read()
-    assert "NUM_GPUS=${1:-1}" in rb and "DTYPE=${2:-bfloat16}" in rb
-    assert "NUM_GPUS=${1:-2}" in rs and "MODE=${2:-independent}" in rs and "DTYPE=${3:-bfloat16}" in rs
-    for text in (rb, rs):
-        assert "--sizes 4096 8192 16384 --iterations 50 --warmup 10" in text
-        assert "torch.distributed.run" in text and "--nproc_per_node=$NUM_GPUS" in text
-    assert "--master_port=29500" in rb and "--master_port=29503" in rs
-    for script in ("run_benchmark.sh", "run_scaling_benchmark.sh"):
+    """run_benchmark.sh: NUM_GPUS [DTYPE] (defaults 1 / bfloat16, port 29500); run_scaling_benchmark.sh:
+    NUM_GPUS [MODE] [DTYPE] (2 / independent / bfloat16, port 29503) — same sweep, same banner lines."""
+    out = _dry_run("run_benchmark.sh")
+    assert "Starting distributed matrix multiplication benchmark with 1 GPU(s)\nData type: bfloat16\n" in out
+    assert "Running in single GPU mode..." in out
+    assert "CMD: python3 matmul_benchmark.py --sizes 4096 8192 16384 --iterations 50 --warmup 10 --dtype bfloat16" in out
+    out = _dry_run("run_benchmark.sh", "4", "float16", "--check")
+    assert "Running in distributed mode with 4 GPUs..." in out
+    assert "torch.distributed.run" in out and "--nproc_per_node=4" in out and "--master_port=29500" in out
+    assert out.strip().endswith("--dtype float16 --check")
+    out = _dry_run("run_scaling_benchmark.sh")
+    assert "Matrix Multiplication Scaling Benchmark\n  GPUs: 2\n  Mode: independent (independent, batch_parallel, matrix_parallel)\n  Data type: bfloat16\n" in out
+    assert "--nproc_per_node=2" in out and "--master_port=29503" in out
+    assert "matmul_scaling_benchmark.py --sizes 4096 8192 16384 --iterations 50 --warmup 10 --mode independent --dtype bfloat16" in out
+    out = _dry_run("run_scaling_benchmark.sh", "1", "matrix_parallel", "float32")
+    assert "CMD: python3 matmul_scaling_benchmark.py" in out and "--mode matrix_parallel --dtype float32" in out
+    for script in ("run_benchmark.sh", "run_scaling_benchmark.sh", "run_overlap_benchmark.sh", "run_common.sh"):
         subprocess.check_call(["bash", "-n", os.path.join(ROOT, script)])
 
 
@@ -142,7 +160,7 @@ def test_overlap_report_text_matches_reference(host_logic, mode):
 
 
 def test_overlap_launcher_keeps_the_reference_positionals():
-    text = open(os.path.join(ROOT, "run_overlap_benchmark.sh")).read()
-    assert "NUM_GPUS=${1:-2}" in text and "MODE=${2:-overlap}" in text and "DTYPE=${3:-bfloat16}" in text
-    assert "--master_port=29502" in text and "--sizes 4096 8192 16384 --iterations 50 --warmup 10" in text
-    subprocess.check_call(["bash", "-n", os.path.join(ROOT, "run_overlap_benchmark.sh")])
+    out = _dry_run("run_overlap_benchmark.sh")
+    assert "Starting overlapped communication/computation benchmark\n  GPUs: 2\n  Mode: overlap (no_overlap, overlap, pipeline)\n  Data type: bfloat16\n" in out
+    assert "--master_port=29502" in out
+    assert "matmul_overlap_benchmark.py --sizes 4096 8192 16384 --iterations 50 --warmup 10 --mode overlap --dtype bfloat16" in out

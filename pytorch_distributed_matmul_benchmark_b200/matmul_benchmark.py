@@ -134,7 +134,7 @@ def main(argv: Optional[List[str]] = None) -> None:
     dtype = hostlib.DTYPE_MAP[args.dtype]
     rank, world_size = setup_distributed()
     if rank == 0:
-        hostlib.print_banner(show_memory_first=True)
+        hostlib.print_banner()
     results: list = []
     try:
         run_benchmarks(rank, world_size, args.sizes, dtype, args.iterations, args.warmup, check=args.check,

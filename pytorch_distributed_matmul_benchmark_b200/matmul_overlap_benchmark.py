@@ -233,7 +233,7 @@ def main(argv: Optional[List[str]] = None) -> None:
     mode = BenchmarkMode(args.mode)
     rank, world_size = setup_distributed()
     if rank == 0:
-        hostlib.print_banner(show_memory_first=False)
+        hostlib.print_banner()
         if torch.cuda.is_available() and torch.cuda.device_count() > 1:
             print("\nChecking GPU interconnect...")
             print("  Multi-GPU system detected. Use nvidia-smi topo -m for interconnect details.")

@@ -383,7 +383,7 @@ def main(argv: Optional[List[str]] = None) -> None:
     mode = ScalingMode(args.mode)
     rank, world_size = setup_distributed()
     if rank == 0:
-        hostlib.print_banner(show_memory_first=False)
+        hostlib.print_banner()
     device = hostlib.rank_device(rank)
     ops = hostlib.device_ops(rank, world_size, device)
     if world_size > 1 and not verify_collectives(rank, world_size, device, ops):

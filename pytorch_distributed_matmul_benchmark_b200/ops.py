@@ -157,7 +157,9 @@ class HostGemm:
                 raise RuntimeError("HostGemm takes pinned host tensors")
         main = torch.cuda.current_stream(self.device)
         rows = self.M // self.panels
-        self.up.wait_stream(main)    # the previous call's GEMMs no longer read dA / dB
+        # dA / dB may be refilled as soon as the previous call's last GEMM has read them; its C may still be on
+        # its way down (the copy engines are independent), so back-to-back calls overlap by that tail
+        self.up.wait_event(self.ev_c[-1])
         self.down.wait_stream(main)
         with torch.cuda.stream(self.up):
             self.dB.copy_(hB, non_blocking=True)

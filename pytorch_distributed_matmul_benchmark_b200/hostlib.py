@@ -73,7 +73,8 @@ def rank_device(rank: int) -> str:
     return f"cuda:{rank % torch.cuda.device_count()}"
 
 
-def print_banner(show_memory_first: bool) -> None:
+def print_banner() -> None:
+    """Version / device banner of the reference mains (matmul_benchmark.py:178-190, matmul_scaling_benchmark.py:376-386)."""
     print(f"PyTorch version: {torch.__version__}")
     print(f"CUDA available: {torch.cuda.is_available()}")
     if torch.cuda.is_available():

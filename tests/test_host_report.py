@@ -164,3 +164,8 @@ def test_overlap_launcher_keeps_the_reference_positionals():
     assert "Starting overlapped communication/computation benchmark\n  GPUs: 2\n  Mode: overlap (no_overlap, overlap, pipeline)\n  Data type: bfloat16\n" in out
     assert "--master_port=29502" in out
     assert "matmul_overlap_benchmark.py --sizes 4096 8192 16384 --iterations 50 --warmup 10 --mode overlap --dtype bfloat16" in out
+
+
+def test_banner_runs_without_a_gpu():
+    out = _capture(hostlib.print_banner)
+    assert out.startswith("PyTorch version: ") and "CUDA available: " in out

@@ -151,6 +151,25 @@ def split_columns(matrix_size: int, world_size: int, rank: int) -> Tuple[int, in
     return start, (start + per if rank < world_size - 1 else matrix_size)
 
 
+def slab_pitch(matrix_size: int, world_size: int) -> int:
+    """Row pitch (elements) of every rank's column-slab storage: the widest slab, rounded up to 16 bytes of any dtype.
+
+    Equal to the slab width when matrix_size % (8 * world_size) == 0 (then nothing is padded); otherwise the
+    unequal slabs of split_columns travel through equal-size storage, which is what all_gather needs.
+    """
+    widest = matrix_size - (world_size - 1) * (matrix_size // world_size)
+    return (widest + 7) // 8 * 8
+
+
+def assemble_slabs(slabs: torch.Tensor, matrix_size: int, world_size: int) -> torch.Tensor:
+    """[world][N][pitch] gathered storage -> the N x N product (slab r holds the columns of rank r)."""
+    parts = []
+    for r in range(world_size):
+        s, e = split_columns(matrix_size, world_size, r)
+        parts.append(slabs[r, :, :e - s])
+    return torch.cat(parts, dim=1)
+
+
 def add_common_args(parser) -> None:
     parser.add_argument("--sizes", type=int, nargs="+", default=list(DEFAULT_SIZES),
                         help="Matrix sizes to benchmark (default: 4096 8192 16384)")

@@ -197,32 +197,38 @@ def benchmark_matrix_parallel(matrix_size: int, dtype: torch.dtype, device: str,
     if world_size == 1:
         return benchmark_independent(matrix_size, dtype, device, rank, num_iterations, warmup_iterations, ops=ops,
                                      check=check)
-    if matrix_size % world_size:
-        # the reference fails here too: its last rank's slab is wider and all_gather rejects the shapes (:179-183,:219-221)
-        raise RuntimeError(f"matrix_parallel needs matrix_size % world_size == 0 (got {matrix_size} % {world_size})")
     start_col, end_col = hostlib.split_columns(matrix_size, world_size, rank)
+    width, pitch = end_col - start_col, hostlib.slab_pitch(matrix_size, world_size)
+    if pitch != width and (overlap or fused):
+        raise RuntimeError(f"--overlap/--fused need equal, 16-byte-pitched column slabs: matrix_size % {8 * world_size} == 0 "
+                           f"(got {matrix_size})")
+    # pitch == width whenever matrix_size % (8 * world) == 0: plain contiguous slabs.  Otherwise (the reference
+    # breaks inside all_gather on its unequal slabs, :179-183,:219-221) every rank keeps its slab in storage of
+    # the common pitch, so that the gather moves equal-size pieces and B_local / C_local rows stay 16-byte aligned.
     torch.manual_seed(0)
     A = torch.randn(matrix_size, matrix_size, dtype=dtype, device=device)
+    B_store = torch.zeros(matrix_size, pitch, dtype=dtype, device=device)
     if check:
         B_full = torch.randn(matrix_size, matrix_size, dtype=dtype, device=device)
-        B_local = B_full[:, start_col:end_col].contiguous()
+        B_store[:, :width] = B_full[:, start_col:end_col]
     else:
         B_full = None
         torch.manual_seed(1000 + rank)
-        B_local = torch.randn(matrix_size, end_col - start_col, dtype=dtype, device=device)
-    C_local = torch.empty(matrix_size, end_col - start_col, dtype=dtype, device=device)
-    slabs = torch.zeros(world_size, matrix_size, end_col - start_col, dtype=dtype, device=device)
+        B_store[:, :width] = torch.randn(matrix_size, width, dtype=dtype, device=device)
+    C_store = torch.zeros(matrix_size, pitch, dtype=dtype, device=device)
+    B_local, C_local = B_store[:, :width], C_store[:, :width]
+    slabs = torch.zeros(world_size, matrix_size, pitch, dtype=dtype, device=device)
 
     for _ in range(warmup_iterations):
         ops.matmul(A, B_local, out=C_local)
-        ops.all_gather_into(slabs, C_local)
+        ops.all_gather_into(slabs, C_store)
     ops.synchronize()
     dist.barrier()
 
     compute_ms = comm_ms = 0.0
     for _ in range(num_iterations):
         compute_ms += _timed(ops, lambda: ops.matmul(A, B_local, out=C_local))
-        comm_ms += _timed(ops, lambda: ops.all_gather_into(slabs, C_local))
+        comm_ms += _timed(ops, lambda: ops.all_gather_into(slabs, C_store))
     avg_compute_time = (compute_ms / 1000.0) / max(num_iterations, 1)
     avg_comm_time = (comm_ms / 1000.0) / max(num_iterations, 1)
     avg_total_time = avg_compute_time + avg_comm_time
@@ -258,7 +264,7 @@ def benchmark_matrix_parallel(matrix_size: int, dtype: torch.dtype, device: str,
 
     if check and B_full is not None:
         ops.synchronize()
-        C_global = torch.cat(list(slabs.unbind(0)), dim=1)  # [N][N]: slab r holds columns of rank r
+        C_global = hostlib.assemble_slabs(slabs, matrix_size, world_size)  # [N][N]: slab r holds columns of rank r
         _report_check(rank, hostlib.parity_error(C_global, A, B_full), dtype)
 
     tflops_per_gpu = calculate_tflops(matrix_size, avg_total_time, num_ops=1) / world_size

@@ -18,6 +18,7 @@ import torch.distributed as dist  # noqa: E402
 from oracle import oracle, reference_port  # noqa: E402
 from pytorch_distributed_matmul_benchmark_b200 import hostlib  # noqa: E402
 from pytorch_distributed_matmul_benchmark_b200 import matmul_scaling_benchmark as ms  # noqa: E402
+from pytorch_distributed_matmul_benchmark_b200 import matmul_distributed_benchmark as md  # noqa: E402
 
 
 class FakeEvent:
@@ -81,8 +82,12 @@ def main(out_dir: str):
         for mode in ms.ScalingMode:
             ms.run_benchmarks(rank, ws, [32, 64], torch.float32, mode, 2, 1, ops=ops, device=device, check=True)
         ms.run_benchmarks(rank, ws, [30], torch.bfloat16, ms.ScalingMode.MATRIX_PARALLEL, 1, 1, ops=ops, device=device)
-        ms.run_benchmarks(rank, ws, [33], torch.float32, ms.ScalingMode.MATRIX_PARALLEL, 1, 1, ops=ops, device=device)
+        ms.run_benchmarks(rank, ws, [33], torch.float32, ms.ScalingMode.MATRIX_PARALLEL, 1, 1, ops=ops, device=device, check=True)
+        ms.run_benchmarks(rank, ws, [33], torch.float32, ms.ScalingMode.MATRIX_PARALLEL, 1, 1, ops=ops, device=device, fused=True)
         ms.run_benchmarks(rank, 8, [32], torch.float32, ms.ScalingMode.BATCH_PARALLEL, 1, 1, ops=ops, device=device)
+        # the earlier draft's modes (backup/matmul_distributed_benchmark.py); 33 % 2 != 0 exercises the unequal slabs
+        for mode in md.BenchmarkMode:
+            md.run_benchmarks(rank, ws, [32, 33], torch.float32, mode, 2, 1, ops=ops, device=device, check=True)
     finally:
         sys.stdout = real_stdout
         log.close()

@@ -39,6 +39,7 @@ import matmul_benchmark as mb  # noqa: E402
 import matmul_scaling_benchmark as ms  # noqa: E402
 sys.path.insert(0, os.path.join(REF, "backup"))
 import matmul_overlap_benchmark as ov  # noqa: E402
+import matmul_distributed_benchmark as md  # noqa: E402
 
 DT = {"float32": torch.float32, "float16": torch.float16, "bfloat16": torch.bfloat16}
 
@@ -197,6 +198,25 @@ def gen_host_logic():
     finally:
         ov.benchmark_no_overlap, ov.benchmark_overlap, ov.benchmark_pipeline = saved
 
+    # backup/matmul_distributed_benchmark.py (the earlier draft: independent / data_parallel / model_parallel)
+    out["cli_md_default"] = cli(md, [])  # rank, world, sizes, dtype, mode, iters, warmup
+    out["modes_md"] = [m.value for m in md.BenchmarkMode]
+    fake_comm = 0.0015
+    out["fake_comm"] = fake_comm
+    saved = (md.benchmark_independent, md.benchmark_data_parallel, md.benchmark_model_parallel)
+    md.benchmark_independent = lambda size, dtype, device, it, wu: (fake_time, md.calculate_tflops(size, fake_time), 0.0)
+    md.benchmark_data_parallel = lambda size, dtype, device, rank, it, wu: (
+        fake_time + fake_comm, md.calculate_tflops(size, fake_time), fake_comm)
+    md.benchmark_model_parallel = lambda size, dtype, device, rank, ws, it, wu: (
+        fake_time + fake_comm, md.calculate_tflops(size, fake_time + fake_comm), fake_comm)
+    try:
+        for mode in md.BenchmarkMode:
+            for ws in (1, 2):  # no process group here, so ws=2 exercises the report branches only (:251-257)
+                out[f"report_md_{mode.value}_ws{ws}"] = capture_report(
+                    md, lambda mode=mode, ws=ws: md.run_benchmarks(0, ws, [4096, 16384], torch.bfloat16, mode, 50, 10))
+    finally:
+        md.benchmark_independent, md.benchmark_data_parallel, md.benchmark_model_parallel = saved
+
     # The reference's own CPU path, executed here once as a record (config 1 of BASELINE.json, reduced iterations)
     with contextlib.redirect_stdout(io.StringIO()):
         avg, tf = mb.benchmark_matmul(1024, torch.float32, "cpu", 3, 1)
@@ -207,7 +227,8 @@ def gen_host_logic():
 
 
 if __name__ == "__main__":
-    gen_matmul_fixtures()
+    if "--host-only" not in sys.argv:  # the matrix fixtures are deterministic; skip them when only the report goldens change
+        gen_matmul_fixtures()
     torch.set_num_threads(os.cpu_count() or 1)
     gen_host_logic()
     total = sum(os.path.getsize(os.path.join(HERE, f)) for f in os.listdir(HERE))

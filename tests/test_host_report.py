@@ -169,3 +169,51 @@ def test_overlap_launcher_keeps_the_reference_positionals():
 def test_banner_runs_without_a_gpu():
     out = _capture(hostlib.print_banner)
     assert out.startswith("PyTorch version: ") and "CUDA available: " in out
+
+
+# ---- backup/matmul_distributed_benchmark.py: independent / data_parallel / model_parallel -------
+from pytorch_distributed_matmul_benchmark_b200 import matmul_distributed_benchmark as md  # noqa: E402
+
+
+def test_distributed_cli_defaults_match_reference(host_logic):
+    a = md.build_parser().parse_args([])
+    assert [0, 1, a.sizes, str(hostlib.DTYPE_MAP[a.dtype]), a.mode, a.iterations, a.warmup] == host_logic["cli_md_default"]
+    assert [m.value for m in md.BenchmarkMode] == host_logic["modes_md"]
+    with pytest.raises(SystemExit):
+        md.build_parser().parse_args(["--mode", "batch_parallel"])
+
+
+@pytest.mark.parametrize("ws", [1, 2])
+@pytest.mark.parametrize("mode", list(md.BenchmarkMode))
+def test_distributed_report_text_matches_reference(host_logic, mode, ws):
+    t, c = host_logic["fake_time"], host_logic["fake_comm"]
+    stubs = {
+        md.BenchmarkMode.INDEPENDENT: lambda size: (t, hostlib.calculate_tflops(size, t), 0.0),
+        md.BenchmarkMode.DATA_PARALLEL: lambda size: (t + c, hostlib.calculate_tflops(size, t), c),
+        md.BenchmarkMode.MODEL_PARALLEL: lambda size: (t + c, hostlib.calculate_tflops(size, t + c), c),
+    }
+    out = _capture(lambda: md.run_benchmarks(0, ws, [4096, 16384], torch.bfloat16, mode, 50, 10, bench_fns=stubs, device="cpu"))
+    assert out == host_logic[f"report_md_{mode.value}_ws{ws}"]
+
+
+def test_distributed_launcher_keeps_the_reference_positionals():
+    out = _dry_run("run_distributed_benchmark.sh")
+    assert "Starting distributed matrix multiplication benchmark\n  GPUs: 2\n  Mode: data_parallel\n  Data type: bfloat16\n" in out
+    assert "--master_port=29501" in out
+    assert "matmul_distributed_benchmark.py --sizes 4096 8192 16384 --iterations 50 --warmup 10 --mode data_parallel --dtype bfloat16" in out
+    out = _dry_run("run_distributed_benchmark.sh", "1", "model_parallel", "float16")
+    assert "CMD: python3 matmul_distributed_benchmark.py" in out and "--mode model_parallel --dtype float16" in out
+
+
+def test_model_parallel_slab_storage():
+    """Unequal slabs (N % ws != 0, the reference's :123-125 split) travel through equal-pitch storage."""
+    for N, ws in ((200, 3), (33, 2), (4096, 8), (10, 4)):
+        pitch = hostlib.slab_pitch(N, ws)
+        widths = [e - s for s, e in (hostlib.split_columns(N, ws, r) for r in range(ws))]
+        assert pitch % 8 == 0 and pitch >= max(widths) and sum(widths) == N
+        slabs = torch.zeros(ws, N, pitch)
+        full = torch.arange(N * N, dtype=torch.float32).view(N, N)
+        for r in range(ws):
+            s, e = hostlib.split_columns(N, ws, r)
+            slabs[r, :, :e - s] = full[:, s:e]
+        assert torch.equal(hostlib.assemble_slabs(slabs, N, ws), full)

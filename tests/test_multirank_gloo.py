@@ -42,15 +42,30 @@ def test_collectives_and_aggregation(gloo_run):
 def test_report_for_two_ranks(gloo_run):
     _, report, other = gloo_run
     assert "  - Number of GPUs: 2" in report
-    assert report.count("Parity vs float64 reference") >= 6 and "FAIL" not in report
+    assert report.count("Parity vs float64 reference") >= 11 and "FAIL" not in report
     assert "  - Scaling efficiency:" in report and "  - Total system TFLOPS:" in report
     assert "  - Processing 4 total batches across 2 GPU(s)" in report
     assert "  - Each GPU processes 1/2 of the matrix" in report
     assert "    Compute time:" in report and "Comm time:" in report
     assert "Results for 30x30" in report  # 30 % 2 == 0, bf16 rows of 15 elements are fine on the CPU stand-in
-    # N % world != 0: the reference breaks inside all_gather (:179-183,:219-221); here it is a clean ERROR line
-    assert "ERROR: matrix_parallel needs matrix_size % world_size == 0 (got 33 % 2)" in report
+    # N % world != 0: the reference breaks inside all_gather (:179-183,:219-221); here the unequal slabs (16 + 17
+    # columns) are gathered through equal-pitch storage and the assembled product is checked
+    assert "Results for 33x33" in report
+    # ... except for the fused / overlapped variants, which need equal slabs: a clean ERROR line
+    assert "ERROR: --overlap/--fused need equal, 16-byte-pitched column slabs: matrix_size % 16 == 0 (got 33)" in report
     # batch_parallel with total batch 4 at world size 8: local batch 0, 0 TFLOPS, as in the reference (:111)
     assert "  - Processing 4 total batches across 8 GPU(s)" in report and "  - TFLOPS per GPU: 0.00" in report
     # only rank 0 reports (matmul_scaling_benchmark.py:256,269,308)
     assert "Results for" not in other
+
+
+def test_distributed_draft_modes_for_two_ranks(gloo_run):
+    """independent / data_parallel / model_parallel of backup/matmul_distributed_benchmark.py, world size 2."""
+    _, report, other = gloo_run
+    part = report[report.index("Distributed Matrix Multiplication Benchmark"):]
+    assert "FAIL" not in part and "ERROR" not in part
+    assert part.count("Results for 32x32") == 3 and part.count("Results for 33x33") == 3  # 33: unequal slabs 16 + 17
+    assert part.count("Parity of the reduced product vs float64 sum") == 2  # data_parallel, both sizes
+    assert part.count("  - Effective TFLOPS:") == 4 and part.count("  - Total TFLOPS (all GPUs):") == 2
+    assert part.count("  - Communication time:") == 4 and part.count("  - Scaling efficiency:") == 4
+    assert "Distributed Matrix Multiplication Benchmark" not in other

@@ -81,3 +81,22 @@ def test_overlap_script_two_gpus(mode):
     assert "Results for 2048x2048:" in out and "ERROR" not in out and "FAIL" not in out
     assert "Parity of the reduced product" in out and "-> OK" in out
     assert "  - Note: In data parallel, each GPU does full matrix multiply" in out
+
+
+@pytest.mark.parametrize("mode", ["independent", "data_parallel", "model_parallel"])
+def test_distributed_draft_script_single_gpu(mode):
+    out = _run([sys.executable, "matmul_distributed_benchmark.py", "--sizes", "1024", "--iterations", "3", "--warmup", "1",
+                "--mode", mode, "--check"])
+    assert f"  - Mode: {mode}" in out and "Results for 1024x1024:" in out
+    assert "-> OK" in out and "ERROR" not in out and "FAIL" not in out
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("mode,size", [("data_parallel", "2048"), ("model_parallel", "2048"), ("model_parallel", "2056")])
+def test_distributed_draft_script_two_gpus(mode, size):
+    """2056 / 2 = 1028-wide bf16 slabs: a row pitch of 2056 bytes is not a multiple of 16, so this takes the padded-pitch path."""
+    out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                "--master-addr=127.0.0.1", f"--master-port={_free_port()}", "matmul_distributed_benchmark.py", "--sizes",
+                size, "--iterations", "3", "--warmup", "2", "--mode", mode, "--check"])
+    assert f"Results for {size}x{size}:" in out and "ERROR" not in out and "FAIL" not in out and "-> OK" in out
+    assert "  - Communication time:" in out and "  - Scaling efficiency:" in out

@@ -72,7 +72,8 @@ B2MM_API void b2mm_debug_set_trace(void* device_buffer);
 
 /*
  * Bytes of scratch b2mm_gemm needs for this problem (0 for bf16/fp16).
- * fp32 needs room for the TF32 hi/lo split of both operands.
+ * fp32 needs room for the TF32 hi/lo split of both operands: 8 * (M + N) * K' bytes per batch entry,
+ * K' = K rounded up to 4 (16-byte rows), each of the four arrays rounded up to 256 bytes.
  */
 B2MM_API size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype);
 
@@ -89,8 +90,9 @@ B2MM_API size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64
  *   dtype: b2mm_dtype, same for A, B and C.
  *
  * Requirements: pointers 16-byte aligned; lda/ldb/ldc and batch strides
- * multiples of 16 bytes; M, N, K >= 1 (batch == 0 is a no-op, matching
- * torch.bmm on empty tensors — matmul_scaling_benchmark.py:111 at ws=8).
+ * multiples of 16 bytes.  M, N, K themselves are free.  batch == 0, M == 0 or N == 0 is a no-op
+ * (torch.bmm on empty tensors — matmul_scaling_benchmark.py:111 at ws=8); K == 0 zero-fills C
+ * (an empty sum, as torch.matmul returns).
  * Rows/columns/K that do not fill a tile are handled in-kernel (TMA
  * zero-fill / clipped stores); nothing is padded by the caller.
  *
@@ -171,10 +173,14 @@ B2MM_API int b2mm_all_gather(void* comm, const void* send, void* recv_slabs,
  * travel over the existing process group; every other rank imports them with ITS device current and
  * gets a pointer its kernels can load/store through NVLink.  No counterpart in the reference (torch's
  * NCCL process group does the equivalent internally for dist.all_gather, matmul_scaling_benchmark.py:221).
- * Imported mappings live until process exit. */
+ * An allocation is mapped once per process and reference counted: every b2mm_ipc_import must be paired
+ * with one b2mm_ipc_release of the same handle, and the last release unmaps it.  All importers must have
+ * released (and their kernels finished) BEFORE the owner frees the allocation — CUDA leaves the other
+ * order undefined — so callers put a cross-rank barrier between the releases and the free. */
 #define B2MM_IPC_HANDLE_BYTES 64
 B2MM_API int b2mm_ipc_export(const void* ptr, void* handle_out_64_bytes, int64_t* offset_out);
 B2MM_API int b2mm_ipc_import(const void* handle_64_bytes, int64_t offset, void** ptr_out);
+B2MM_API int b2mm_ipc_release(const void* handle_64_bytes);
 
 /* Cross-rank barrier on `stream` (a one-word ncclAllReduce): everything enqueued on `stream` before
  * it, on every rank, has completed before anything after it starts, on any rank.  Stands where the

@@ -256,8 +256,9 @@ static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 size_t gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype) {
   if (dtype != B2MM_FP32 || batch <= 0) return 0;
-  const size_t a = align_up((size_t)batch * M * K * 4, 256);
-  const size_t b = align_up((size_t)batch * K * N * 4, 256);
+  const size_t kp = align_up((size_t)K, 4);  // packed rows of the hi/lo splits keep a 16-byte pitch for TMA
+  const size_t a = align_up((size_t)batch * M * kp * 4, 256);
+  const size_t b = align_up((size_t)batch * N * kp * 4, 256);
   return 2 * a + 2 * b;
 }
 
@@ -278,7 +279,16 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
   if (es == 0) return fail(B2MM_ERR_BAD_ARG, "unknown dtype %d", dtype);
   if (batch < 0 || M < 0 || N < 0 || K < 0) return fail(B2MM_ERR_BAD_ARG, "negative size");
   if (batch == 0 || M == 0 || N == 0) return B2MM_OK;  // empty output: nothing to do (torch.bmm on b=0)
-  if (K == 0) return fail(B2MM_ERR_UNSUPPORTED, "K == 0 (zero-fill of C) is not implemented");
+  if (K == 0) {  // an empty sum: C = 0, as torch.matmul gives for (M x 0) @ (0 x N)
+    if (fanout > 0) return fail(B2MM_ERR_UNSUPPORTED, "K == 0 with remote destinations");
+    if (!C) return fail(B2MM_ERR_BAD_ARG, "null operand pointer");
+    if (ldc < N) return fail(B2MM_ERR_BAD_ARG, "leading dimension smaller than row length");
+    for (int64_t b = 0; b < batch; ++b) {
+      cudaError_t e = cudaMemset2DAsync((char*)C + (size_t)b * sC * es, (size_t)ldc * es, 0, (size_t)N * es, (size_t)M, stream);
+      if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "zero-fill of C failed: %s", cudaGetErrorString(e));
+    }
+    return B2MM_OK;
+  }
   if (!A || !B || !C) return fail(B2MM_ERR_BAD_ARG, "null operand pointer");
   if (lda < K || ldb < N || ldc < N) return fail(B2MM_ERR_BAD_ARG, "leading dimension smaller than row length");
   if (((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) return fail(B2MM_ERR_UNSUPPORTED, "operands must be 16-byte aligned");
@@ -301,21 +311,22 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
     if (!workspace || workspace_bytes < need)
       return fail(B2MM_ERR_WORKSPACE, "fp32 GEMM needs %zu bytes of workspace, got %zu", need, workspace_bytes);
     if ((uintptr_t)workspace & 255) return fail(B2MM_ERR_BAD_ARG, "workspace must be 256-byte aligned");
-    const size_t a_bytes = align_up((size_t)batch * M * K * 4, 256);
-    const size_t b_bytes = align_up((size_t)batch * K * N * 4, 256);
+    const int64_t kp = (int64_t)align_up((size_t)K, 4);
+    const size_t a_bytes = align_up((size_t)batch * M * kp * 4, 256);
+    const size_t b_bytes = align_up((size_t)batch * N * kp * 4, 256);
     char* w = (char*)workspace;
     float* a_hi = (float*)w;
     float* a_lo = (float*)(w + a_bytes);
     float* b_hi = (float*)(w + 2 * a_bytes);
     float* b_lo = (float*)(w + 2 * a_bytes + b_bytes);
     const int blocks = (sms > 0 ? sms : 148) * 8;
-    split_tf32_kernel<<<blocks, 256, 0, stream>>>((const float*)A, a_hi, a_lo, M, K, lda, batch, sA);
-    split_tf32_transpose_kernel<<<blocks, 256, 0, stream>>>((const float*)B, b_hi, b_lo, K, N, ldb, batch, sB);
+    split_tf32_kernel<<<blocks, 256, 0, stream>>>((const float*)A, a_hi, a_lo, M, K, lda, kp, batch, sA);
+    split_tf32_transpose_kernel<<<blocks, 256, 0, stream>>>((const float*)B, b_hi, b_lo, K, N, ldb, kp, batch, sB);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "split launch failed: %s", cudaGetErrorString(e));
     count_launch(2);
-    o.A = a_hi; o.A_lo = a_lo; o.lda = K; o.sA = M * K;
-    o.B = b_hi; o.B_lo = b_lo; o.ldb = K; o.sB = K * N;  // B^T: N x K, packed
+    o.A = a_hi; o.A_lo = a_lo; o.lda = kp; o.sA = M * kp;
+    o.B = b_hi; o.B_lo = b_lo; o.ldb = kp; o.sB = N * kp;  // B^T: N x K, packed
     // 256 x 128 tiles, tensor-core accumulation in chunks of 8 k-blocks (K = 256), fp32 register carry.
     return launch_cfg<GemmConfig<2, 128, 4, 2, float, /*kBKMajor=*/true, /*kMBlocks=*/1, /*kChunkKB=*/8>>(o, max_sms, stream);
   }

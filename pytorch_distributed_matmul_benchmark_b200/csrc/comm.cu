@@ -66,7 +66,7 @@ static constexpr int kMaxPanels = 64;
 struct Comm {
   ncclComm_t nccl = nullptr;
   int rank = 0, world = 1;
-  cudaEvent_t panel_done[kMaxPanels];
+  cudaEvent_t panel_done[kMaxPanels] = {};
   cudaEvent_t comm_done = nullptr;
   float* barrier_word = nullptr;  // 1 float on the device: payload of b2mm_comm_barrier
   int ready_epoch = 0;            // fused all_reduce: panels announced so far (same sequence on every rank)
@@ -145,17 +145,19 @@ int b2mm_comm_init(const void* id_bytes, int rank, int world, void** comm_out) {
     r = nccl().CommInitRank(&c->nccl, world, id, rank);
   }
   if (r != ncclSuccess) {
-    delete c;
+    c->nccl = nullptr;
+    b2mm_comm_destroy(c);
     return nccl_fail("ncclCommInitRank", r);
   }
-  for (int i = 0; i < kMaxPanels; ++i)
-    if (cudaEventCreateWithFlags(&c->panel_done[i], cudaEventDisableTiming) != cudaSuccess) {
-      delete c;
-      return fail(B2MM_ERR_CUDA, "cudaEventCreate failed");
-    }
-  cudaEventCreateWithFlags(&c->comm_done, cudaEventDisableTiming);
+  bool ok = cudaEventCreateWithFlags(&c->comm_done, cudaEventDisableTiming) == cudaSuccess;
+  for (int i = 0; ok && i < kMaxPanels; ++i)
+    ok = cudaEventCreateWithFlags(&c->panel_done[i], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) {
+    b2mm_comm_destroy(c);  // releases whatever was created so far
+    return fail(B2MM_ERR_CUDA, "cudaEventCreate failed");
+  }
   if (cudaMalloc(&c->barrier_word, 256) != cudaSuccess || cudaMemset(c->barrier_word, 0, 256) != cudaSuccess) {
-    delete c;
+    b2mm_comm_destroy(c);
     return fail(B2MM_ERR_CUDA, "cudaMalloc(barrier word) failed");
   }
   *comm_out = c;
@@ -165,7 +167,8 @@ int b2mm_comm_init(const void* id_bytes, int rank, int world, void** comm_out) {
 int b2mm_comm_destroy(void* comm) {
   if (!comm) return B2MM_OK;
   Comm* c = (Comm*)comm;
-  for (int i = 0; i < kMaxPanels; ++i) cudaEventDestroy(c->panel_done[i]);
+  for (int i = 0; i < kMaxPanels; ++i)
+    if (c->panel_done[i]) cudaEventDestroy(c->panel_done[i]);
   if (c->comm_done) cudaEventDestroy(c->comm_done);
   if (c->barrier_word) cudaFree(c->barrier_word);
   if (c->nccl) nccl().CommDestroy(c->nccl);
@@ -201,9 +204,11 @@ namespace {
 struct IpcEntry {
   cudaIpcMemHandle_t h;
   void* base;
+  int refs;
 };
 std::mutex g_ipc_mu;
-IpcEntry g_ipc_open[64];
+constexpr int kMaxIpcOpen = 256;
+IpcEntry g_ipc_open[kMaxIpcOpen];
 int g_ipc_n = 0;
 
 using GetRangeFn = int (*)(unsigned long long*, size_t*, unsigned long long);
@@ -244,18 +249,36 @@ int b2mm_ipc_import(const void* handle_64_bytes, int64_t offset, void** ptr_out)
   std::lock_guard<std::mutex> lock(g_ipc_mu);
   for (int i = 0; i < g_ipc_n; ++i)  // an allocation can be opened only once per process
     if (!memcmp(&g_ipc_open[i].h, &h, sizeof(h))) {
+      ++g_ipc_open[i].refs;
       *ptr_out = (char*)g_ipc_open[i].base + offset;
       return B2MM_OK;
     }
-  if (g_ipc_n == 64) return fail(B2MM_ERR_UNSUPPORTED, "too many imported allocations");
+  if (g_ipc_n == kMaxIpcOpen) return fail(B2MM_ERR_UNSUPPORTED, "too many imported allocations (%d open); release some", kMaxIpcOpen);
   void* base = nullptr;
   cudaError_t e = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
   if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
   g_ipc_open[g_ipc_n].h = h;
   g_ipc_open[g_ipc_n].base = base;
+  g_ipc_open[g_ipc_n].refs = 1;
   ++g_ipc_n;
   *ptr_out = (char*)base + offset;
   return B2MM_OK;
+}
+
+int b2mm_ipc_release(const void* handle_64_bytes) {
+  if (!handle_64_bytes) return fail(B2MM_ERR_BAD_ARG, "null handle");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle_64_bytes, sizeof(h));
+  std::lock_guard<std::mutex> lock(g_ipc_mu);
+  for (int i = 0; i < g_ipc_n; ++i)
+    if (!memcmp(&g_ipc_open[i].h, &h, sizeof(h))) {
+      if (--g_ipc_open[i].refs > 0) return B2MM_OK;
+      cudaError_t e = cudaIpcCloseMemHandle(g_ipc_open[i].base);
+      g_ipc_open[i] = g_ipc_open[--g_ipc_n];
+      if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "cudaIpcCloseMemHandle: %s", cudaGetErrorString(e));
+      return B2MM_OK;
+    }
+  return fail(B2MM_ERR_BAD_ARG, "handle was not imported (or already released)");
 }
 
 int b2mm_comm_barrier(void* comm, b2mm_stream_t stream) {

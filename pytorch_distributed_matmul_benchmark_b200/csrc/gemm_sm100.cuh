@@ -651,15 +651,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // words whose low 13 mantissa bits are zero, so the tensor core's fp32->tf32
 // read is exact whatever its rounding.
 __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo,
-                                  int64_t rows, int64_t cols, int64_t ld, int64_t batch, int64_t stride) {
-  const int64_t cols4 = cols >> 2;  // cols % 4 == 0 is enforced by the 16-byte ld rule
+                                  int64_t rows, int64_t cols, int64_t ld, int64_t out_ld, int64_t batch,
+                                  int64_t stride) {
+  const int64_t cols4 = (cols + 3) >> 2;  // ld % 4 == 0 (16-byte rule), cols itself is free; out_ld = 4 * cols4
   const int64_t total = batch * rows * cols4;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t c4 = i % cols4;
     const int64_t r = (i / cols4) % rows;
     const int64_t b = i / (cols4 * rows);
-    const float4 v = *reinterpret_cast<const float4*>(x + b * stride + r * ld + c4 * 4);
-    float in[4] = {v.x, v.y, v.z, v.w};
+    const float* src = x + b * stride + r * ld + c4 * 4;
+    float in[4] = {0.f, 0.f, 0.f, 0.f};
+    if (c4 * 4 + 4 <= cols) {
+      const float4 v = *reinterpret_cast<const float4*>(src);
+      in[0] = v.x; in[1] = v.y; in[2] = v.z; in[3] = v.w;
+    } else {  // last, partial group of a row whose length is not a multiple of 4: never read past column cols-1
+      for (int j = 0; j < 4; ++j)
+        if (c4 * 4 + j < cols) in[j] = src[j];
+    }
     float h[4], l[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -670,18 +678,18 @@ __global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict
       asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(rem));
       l[j] = __uint_as_float(lb);
     }
-    const int64_t o = (b * rows + r) * cols + c4 * 4;  // packed output, ld == cols
+    const int64_t o = (b * rows + r) * out_ld + c4 * 4;  // packed output, 16-byte-aligned pitch
     *reinterpret_cast<float4*>(hi + o) = make_float4(h[0], h[1], h[2], h[3]);
     *reinterpret_cast<float4*>(lo + o) = make_float4(l[0], l[1], l[2], l[3]);
   }
 }
 
 // Same split for B, written TRANSPOSED: x is rows x cols (K x N, leading
-// dimension ld); hi/lo are cols x rows (N x K, packed).  32 x 32 tiles go
+// dimension ld); hi/lo are cols x rows (N x K, row pitch out_ld >= rows).  32 x 32 tiles go
 // through shared memory so that both the read and the write are coalesced.
 __global__ void split_tf32_transpose_kernel(const float* __restrict__ x, float* __restrict__ hi,
                                             float* __restrict__ lo, int64_t rows, int64_t cols, int64_t ld,
-                                            int64_t batch, int64_t stride) {
+                                            int64_t out_ld, int64_t batch, int64_t stride) {
   __shared__ float th[32][33];
   __shared__ float tl[32][33];
   const int64_t tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
@@ -708,7 +716,7 @@ __global__ void split_tf32_transpose_kernel(const float* __restrict__ x, float* 
     for (int i = 0; i < 4; ++i) {
       const int64_t c = tc * 32 + ty + 8 * i, r = tr * 32 + tx;  // output row = input column
       if (c < cols && r < rows) {
-        const int64_t o = (b * cols + c) * rows + r;
+        const int64_t o = (b * cols + c) * out_ld + r;
         hi[o] = th[tx][ty + 8 * i];
         lo[o] = tl[tx][ty + 8 * i];
       }

@@ -101,6 +101,7 @@ class Ops:
     shared_like: Optional[Callable] = None  # (t) -> SharedSlabs
     bmm_allreduce_fused: Optional[Callable] = None  # (A, B, shared_C, n_panels) -> C
     all_reduce_sync: Optional[Callable] = None  # (shared, stream=None) -> t; peer-memory all_reduce, co-resident with a GEMM
+    release_shared: Callable = lambda: None  # collective: unmap peer buffers before their owners free them
     synchronize: Callable = torch.cuda.synchronize
     event: Callable = lambda: torch.cuda.Event(enable_timing=True)
     destroy: Callable = lambda: None
@@ -126,6 +127,7 @@ def device_ops(rank: int, world_size: int, device: str) -> Ops:
         shared_like=comm.shared_like if comm else None,
         bmm_allreduce_fused=comm.bmm_allreduce_fused if comm else None,
         all_reduce_sync=comm.all_reduce_sync if comm else None,
+        release_shared=comm.release_shared if comm else (lambda: None),
         destroy=comm.destroy if comm else (lambda: None),
     )
 

@@ -213,6 +213,8 @@ def run_benchmarks(rank: int, world_size: int, matrix_sizes: List[int], dtype: t
         except Exception as e:
             if rank == 0:
                 print(f"\n  ERROR: {str(e)}")
+        if ops is not None:
+            ops.release_shared()  # peers unmap this size's shared buffers before empty_cache() frees them
         if torch.cuda.is_available():
             torch.cuda.empty_cache()
         if dist.is_initialized():

@@ -358,6 +358,8 @@ def run_benchmarks(rank: int, world_size: int, matrix_sizes: List[int], dtype: t
         except Exception as e:  # the reference's per-size net (:337-342)
             if rank == 0:
                 print(f"\n  ERROR: {str(e)}")
+        if ops is not None:
+            ops.release_shared()  # peers unmap this size's shared buffers before empty_cache() frees them
         if torch.cuda.is_available():
             from . import ops as b2
             b2.release_workspaces()

@@ -84,8 +84,6 @@ def matmul(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None)
     code = _dtype_code(A)
     if M == 0 or N == 0:
         return out
-    if K == 0:
-        return out.zero_()
     ws, ws_bytes = workspace_for(M, N, K, 1, code, A.device)
     with torch.cuda.device(A.device):
         _lib.check(_lib.load().b2mm_gemm(
@@ -116,8 +114,6 @@ def bmm(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None) ->
     code = _dtype_code(A)
     if b == 0 or M == 0 or N == 0:
         return out
-    if K == 0:
-        return out.zero_()
     ws, ws_bytes = workspace_for(M, N, K, b, code, A.device)
     with torch.cuda.device(A.device):
         _lib.check(_lib.load().b2mm_gemm(
@@ -181,10 +177,23 @@ class HostGemm:
 
 
 class SharedSlabs:
-    """A rank's gather buffer plus the pointers under which every rank's buffer is visible here."""
+    """A rank's buffer plus the pointers under which every rank's buffer is visible here.
 
-    def __init__(self, local: torch.Tensor, peer_ptrs, keepalive):
-        self.local, self.peer_ptrs, self._keepalive = local, peer_ptrs, keepalive
+    The peer mappings are reference-counted imports held by libb2mm.so; `close()` gives them back.  Peers must
+    close before the owner's memory is freed, so Communicator keeps every SharedSlabs it made alive until
+    `release_shared()` has closed them on all ranks and passed a barrier.
+    """
+
+    def __init__(self, local: torch.Tensor, peer_ptrs, imported_handles: List[bytes]):
+        self.local, self.peer_ptrs, self._imported = local, peer_ptrs, imported_handles
+
+    def close(self) -> None:
+        lib = _lib.load()
+        for h in self._imported:
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+            _lib.check(lib.b2mm_ipc_release(ctypes.cast(buf, ctypes.c_void_p)))
+        self._imported = []
+        self.peer_ptrs = None
 
 
 class Communicator:
@@ -210,9 +219,30 @@ class Communicator:
             _lib.check(lib.b2mm_comm_init(ctypes.cast(id_buf, ctypes.c_void_p), rank, world_size,
                                           ctypes.byref(self._comm)))
         self.comm_stream = torch.cuda.Stream(device=device, priority=-1)
+        self._shared: List[SharedSlabs] = []
+        self._signals: Optional[SharedSlabs] = None
+
+    def release_shared(self) -> None:
+        """Unmap every buffer handed out by share() / shared_slabs() / shared_like() and let the owners free them.
+
+        Collective: every rank calls it at the same point (the scripts do after each matrix size, before
+        torch.cuda.empty_cache()).  Order: this rank's kernels finish, its imports are closed, all ranks meet at a
+        barrier, and only then are the local tensors dropped — an owner never frees memory a peer still maps.
+        """
+        import torch.distributed as dist
+        torch.cuda.synchronize(self.device)
+        for sh in self._shared:
+            sh.close()
+        if dist.is_initialized():  # unconditional: ranks may disagree on whether anything was shared after an error
+            dist.barrier()
+        self._shared = []
 
     def destroy(self) -> None:
         if self._comm:
+            if self._signals is not None:
+                self._shared.append(self._signals)
+                self._signals = None
+            self.release_shared()
             _lib.check(_lib.load().b2mm_comm_destroy(self._comm))
             self._comm = ctypes.c_void_p()
 
@@ -246,7 +276,7 @@ class Communicator:
         """Cross-rank barrier on the current stream (dist.barrier() for enqueued work)."""
         _lib.check(_lib.load().b2mm_comm_barrier(self._comm, _stream_ptr()))
 
-    def share(self, local: torch.Tensor) -> "SharedSlabs":
+    def share(self, local: torch.Tensor, track: bool = True) -> "SharedSlabs":
         """Map every rank's `local` (same shape on all ranks) into every other rank (CUDA IPC over NVLink).
 
         torch allocates (device memory is torch's business); the 64-byte handles travel through the
@@ -259,7 +289,7 @@ class Communicator:
         _lib.check(lib.b2mm_ipc_export(local.data_ptr(), ctypes.cast(handle, ctypes.c_void_p), ctypes.byref(offset)))
         gathered = [None] * self.world_size
         dist.all_gather_object(gathered, (bytes(handle), offset.value))
-        ptrs = []
+        ptrs, imported = [], []
         with torch.cuda.device(self.device):
             for r, (h, off) in enumerate(gathered):
                 if r == self.rank:
@@ -269,7 +299,11 @@ class Communicator:
                     buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
                     _lib.check(lib.b2mm_ipc_import(ctypes.cast(buf, ctypes.c_void_p), off, ctypes.byref(p)))
                     ptrs.append(p.value)
-        return SharedSlabs(local, (ctypes.c_void_p * self.world_size)(*ptrs), [local])
+                    imported.append(h)
+        shared = SharedSlabs(local, (ctypes.c_void_p * self.world_size)(*ptrs), imported)
+        if track:
+            self._shared.append(shared)
+        return shared
 
     def shared_slabs(self, M: int, n_local: int, dtype: torch.dtype) -> "SharedSlabs":
         """A [world][M][n_local] gather buffer on every rank, each visible to every other rank."""
@@ -298,10 +332,10 @@ class Communicator:
         return shared_C.local
 
     def _signal_pads(self) -> "SharedSlabs":
-        if getattr(self, "_signals", None) is None:
+        if self._signals is None:
             pad = torch.zeros(64, dtype=torch.int32, device=self.device)
             torch.cuda.synchronize(self.device)
-            self._signals = self.share(pad)
+            self._signals = self.share(pad, track=False)  # lives as long as the communicator
             self._band_counters = torch.zeros(256, dtype=torch.int32, device=self.device)
         return self._signals
 

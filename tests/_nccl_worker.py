@@ -96,6 +96,22 @@ def main(out_path):
     comm.all_reduce(Cn)
     torch.cuda.synchronize()
     res["fused_allreduce_vs_nccl"] = rel(shC.local, Cn.double()) <= (ws - 1) * TOL[torch.bfloat16]
+    # share -> use -> release -> free, more often than the import table is long: mappings are given back (an owner
+    # never frees memory a peer still maps) and a freed-and-reallocated block can be shared again
+    ok = True
+    for i in range(300):  # the table holds 256 open allocations
+        sh = comm.shared_like(torch.empty(6 * 1024 * 1024, dtype=torch.bfloat16, device=dev))  # 12 MiB: its own block
+        sh.local.fill_(float(rank + 1))
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.all_reduce_p2p(sh)
+        if i % 50 == 0:
+            torch.cuda.synchronize()
+            ok = ok and bool(torch.all(sh.local == float(ws * (ws + 1) // 2)))
+        del sh
+        comm.release_shared()
+        torch.cuda.empty_cache()
+    res["share_release_cycles"] = ok
     res["launches"] = _lib.launch_count()
 
     comm.destroy()

@@ -146,6 +146,32 @@ def test_empty_and_error_cases():
     assert rc == _lib.ERR_WORKSPACE and b"workspace" in lib.b2mm_last_error()
 
 
+@pytest.mark.parametrize("dname", list(DTYPES))
+def test_k_that_is_not_a_multiple_of_the_vector_width(dname):
+    """K, N, M are free as long as the row PITCH is 16-byte aligned: K = 10 / 1030 inside wider rows.  For fp32
+    this goes through the split pre-pass, whose packed rows are padded to 4 floats (TMA zero-fills past K)."""
+    dt = DTYPES[dname]
+    for M, N, K in ((33, 21, 10), (130, 77, 1030), (5, 3, 1)):
+        torch.manual_seed(K)
+        Aw = torch.randn(M, K + 16 - K % 8, dtype=dt)  # wide rows: slice on the device to keep the padded pitch
+        Bw = torch.randn(K, N + 16 - N % 8, dtype=dt)
+        out = torch.full((M, N + 16 - N % 8), 7.0, dtype=dt, device=DEV)
+        b2.matmul(Aw.to(DEV)[:, :K], Bw.to(DEV)[:, :N], out=out[:, :N])
+        want = oracle.gemm_block_f64(Aw[:, :K].contiguous(), Bw[:, :N].contiguous(), 0, M, 0, N)
+        assert rel_err(out[:, :N], want) <= TOL[dt]
+        assert torch.all(out[:, N:] == 7.0)
+
+
+def test_empty_inner_dimension_zero_fills():
+    """(M x 0) @ (0 x N) is an empty sum: C = 0, written by the library (cudaMemset2DAsync), padding untouched."""
+    for dt in DTYPES.values():
+        out = torch.full((40, 24), 7.0, dtype=dt, device=DEV)
+        C = b2.matmul(torch.empty(40, 0, dtype=dt, device=DEV), torch.empty(0, 16, dtype=dt, device=DEV), out=out[:, :16])
+        assert torch.all(C == 0) and torch.all(out[:, 16:] == 7.0)
+    C = b2.bmm(torch.empty(3, 8, 0, dtype=torch.bfloat16, device=DEV), torch.empty(3, 0, 8, dtype=torch.bfloat16, device=DEV))
+    assert C.shape == (3, 8, 8) and torch.all(C == 0)
+
+
 def test_identity_and_linearity_properties():
     """Size-independent properties: A @ I == A bit-exactly; (A1 + A2) @ B == A1 @ B + A2 @ B to rounding."""
     torch.manual_seed(4)

@@ -94,7 +94,8 @@ B2MM_API size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64
  * (torch.bmm on empty tensors — matmul_scaling_benchmark.py:111 at ws=8); K == 0 zero-fills C
  * (an empty sum, as torch.matmul returns).
  * Rows/columns/K that do not fill a tile are handled in-kernel (TMA
- * zero-fill / clipped stores); nothing is padded by the caller.
+ * zero-fill / clipped stores); nothing is padded by the caller, and nothing outside the M x N
+ * elements of C is written, so C may be a view into a wider matrix.
  *
  * workspace: only read when b2mm_gemm_workspace_bytes(...) > 0.
  */

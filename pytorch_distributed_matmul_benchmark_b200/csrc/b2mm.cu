@@ -193,6 +193,12 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   p.trace = g_trace;
   p.debug_same_k = g_trace ? env_int("B2MM_DEBUG_SAMEK", 0) : 0;  // only together with the trace tool
   p.fanout = o.fanout;
+  p.ragged_n = ((o.N * dtype_bytes(o.dtype)) % 16) != 0;
+  p.c_ptr = o.C;
+  p.ldc = o.ldc;
+  p.c_stride = o.batch > 1 ? o.sC : 0;
+  if (p.ragged_n && (o.fanout > 0 || o.band_counter))
+    return fail(B2MM_ERR_UNSUPPORTED, "the fused collective paths need N * element size to be a multiple of 16 bytes (N=%lld)", (long long)o.N);
   p.max_tiles = o.tiles_per_cluster;
   p.band_counter = o.band_counter;
   p.band_tiles = 1;

@@ -82,7 +82,33 @@ struct GemmParams {
   // this CTA's i-th tile.
   unsigned long long* trace;
   int debug_same_k;  // tools only: every k-block loads k = 0 (all L2 hits; results are meaningless)
+  // Ragged N (N * sizeof(OutT) not a multiple of 16): TMA stores clip at 16-byte granularity (measured: the
+  // whole 16-byte piece holding column N-1 is written), which would clobber up to 15 bytes past column N-1 of
+  // every row.  The one chunk of a tile row that straddles N is therefore written with element stores.
+  int ragged_n;
+  void* c_ptr;             // C as a plain pointer (only used by that element path)
+  long long ldc, c_stride;  // row pitch and batch stride of C, in elements
 };
+
+// Element-exact tail of one staged row (see GemmParams::ragged_n): `n` leading elements of the 128-byte,
+// 128B-swizzled staging row at `srow` (16-byte piece j sits at ((j ^ sw) << 4)) go to dst[0..n).
+// Out of line on purpose: only edge tiles of ragged problems come here, and the main epilogue keeps its registers.
+template <class OutT>
+__device__ __noinline__ void store_row_tail(uint32_t srow, uint32_t sw, OutT* dst, int n) {
+  constexpr int kPer = 16 / (int)sizeof(OutT);
+  for (int e = 0; e < n; ++e) {
+    const uint32_t addr = srow + ((((uint32_t)(e / kPer)) ^ sw) << 4) + (uint32_t)(e % kPer) * (uint32_t)sizeof(OutT);
+    if constexpr (sizeof(OutT) == 4) {
+      uint32_t v;
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+      *reinterpret_cast<uint32_t*>(dst + e) = v;
+    } else {
+      uint16_t v;
+      asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v) : "r"(addr));
+      *reinterpret_cast<uint16_t*>(dst + e) = v;
+    }
+  }
+}
 
 enum class InKind : int { BF16 = 0, FP16 = 1, TF32 = 2 };
 
@@ -489,14 +515,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t tempty_leader = (G == 2) ? mapa(tempty_bar, 0) : tempty_bar;
     uint32_t buf = 0;
 
-    // One 32-row x 128-byte chunk from staging to C — or to every destination of the fan-out.
+    // One 32-row x 128-byte chunk from staging to C — or to every destination of the fan-out.  Called by the
+    // whole warp (lane i staged row i); lane 0 issues the TMA store.
     auto store_chunk = [&](uint32_t sbuf, int col, int row, int b) {
-      if (p.fanout == 0) {
-        tma_store_3d(&tmC, sbuf, col, row, b);
-      } else {
-        for (int d = 0; d < p.fanout; ++d) tma_store_3d(&fan.m[d], sbuf, col, row, b);
+      if (p.ragged_n && col < p.N && col + Cfg::OUT_COLS > p.N) {  // warp-uniform: the chunk that straddles N
+        if (row + (int)lane < p.M)
+          store_row_tail<OutT>(sbuf + lane * 128u, lane & 7u,
+                               static_cast<OutT*>(p.c_ptr) + (size_t)b * p.c_stride + (size_t)(row + (int)lane) * p.ldc + col,
+                               p.N - col);
+        if (lane == 0) tma_store_commit();  // an empty group keeps the wait_read<1> accounting uniform
+        return;
       }
-      tma_store_commit();
+      if (lane == 0) {
+        if (p.fanout == 0) {
+          tma_store_3d(&tmC, sbuf, col, row, b);
+        } else {
+          for (int d = 0; d < p.fanout; ++d) tma_store_3d(&fan.m[d], sbuf, col, row, b);
+        }
+        tma_store_commit();
+      }
     };
 
     // This warp's part of tile (b, m_blk) is complete in global memory: publish it.
@@ -558,9 +595,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) {
-          store_chunk(sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
-        }
+        store_chunk(sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
         buf ^= 1u;
       }
     };
@@ -616,9 +651,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                          __float_as_uint(sum[c * 32 + 4 * j + 3]));
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
-            store_chunk(sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
-          }
+          store_chunk(sbuf, col0 + c * Cfg::OUT_COLS, row0, b);
           buf ^= 1u;
         }
         signal_band(b, m_blk);

@@ -41,6 +41,8 @@ _workspaces = {}
 
 def workspace_for(M: int, N: int, K: int, batch: int, dtype_code: int, device: torch.device):
     """Scratch for the fp32 (3xTF32) path; one cached buffer per device, grown on demand."""
+    if dtype_code != _lib.FP32:  # bf16 / fp16 need none: skip the library call on the hot path
+        return None, 0
     need = int(_lib.load().b2mm_gemm_workspace_bytes(M, N, K, batch, dtype_code))
     if need == 0:
         return None, 0
@@ -60,35 +62,56 @@ def _rows_ok(t: torch.Tensor) -> bool:
     return t.stride(-1) == 1 and t.stride(-2) >= t.shape[-1]
 
 
+def _call_gemm(A, B, out, M, N, K, lda, ldb, ldc, batch, sA, sB, sC, code) -> None:
+    """One b2mm_gemm on the current stream of A's device.  Kept lean: at 2k and below the kernel is shorter
+    than a careless host path (the reference's loop is launch-bound there too)."""
+    ws, ws_bytes = workspace_for(M, N, K, batch, code, A.device)
+    gemm = _lib.load().b2mm_gemm
+    dev = A.device.index
+    if dev == torch.cuda.current_device():
+        rc = gemm(A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, lda, ldb, ldc, batch, sA, sB, sC, code,
+                  ws.data_ptr() if ws is not None else None, ws_bytes, torch.cuda.current_stream().cuda_stream)
+    else:
+        with torch.cuda.device(dev):
+            rc = gemm(A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, lda, ldb, ldc, batch, sA, sB, sC, code,
+                      ws.data_ptr() if ws is not None else None, ws_bytes, torch.cuda.current_stream().cuda_stream)
+    if rc:
+        _lib.check(rc)
+
+
 def matmul(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """C = A @ B for 2-D row-major tensors; allocates C like torch.matmul unless `out` is given."""
     if A.dim() == 3 and B.dim() == 3:
         return bmm(A, B, out=out)
     if A.dim() != 2 or B.dim() != 2:
         raise RuntimeError(f"matmul expects 2-D (or 3-D batched) operands, got {A.dim()}-D and {B.dim()}-D")
-    _require_cuda(A, B)
-    if A.dtype != B.dtype:
+    if not (A.is_cuda and B.is_cuda):
+        _require_cuda(A, B)
+    dtype = A.dtype
+    if dtype != B.dtype:
         raise RuntimeError(f"expected both operands to have the same dtype, got {A.dtype} and {B.dtype}")
     M, K = A.shape
     K2, N = B.shape
     if K != K2:
         raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({M}x{K} and {K2}x{N})")
-    if not _rows_ok(A):
+    code = _DTYPES.get(dtype)
+    if code is None:
+        _dtype_code(A)
+    lda, a1 = A.stride()
+    if a1 != 1 or lda < K:
         A = A.contiguous()
-    if not _rows_ok(B):
+        lda = K
+    ldb, b1 = B.stride()
+    if b1 != 1 or ldb < N:
         B = B.contiguous()
+        ldb = N
     if out is None:
-        out = torch.empty((M, N), dtype=A.dtype, device=A.device)
-    elif out.shape != (M, N) or out.dtype != A.dtype or not _rows_ok(out):
+        out = torch.empty((M, N), dtype=dtype, device=A.device)
+    elif out.shape != (M, N) or out.dtype != dtype or not _rows_ok(out):
         raise RuntimeError("out has the wrong shape, dtype or layout")
-    code = _dtype_code(A)
     if M == 0 or N == 0:
         return out
-    ws, ws_bytes = workspace_for(M, N, K, 1, code, A.device)
-    with torch.cuda.device(A.device):
-        _lib.check(_lib.load().b2mm_gemm(
-            A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, A.stride(0), B.stride(0), out.stride(0),
-            1, 0, 0, 0, code, ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr()))
+    _call_gemm(A, B, out, M, N, K, lda, ldb, out.stride(0), 1, 0, 0, 0, code)
     return out
 
 
@@ -114,12 +137,7 @@ def bmm(A: torch.Tensor, B: torch.Tensor, out: Optional[torch.Tensor] = None) ->
     code = _dtype_code(A)
     if b == 0 or M == 0 or N == 0:
         return out
-    ws, ws_bytes = workspace_for(M, N, K, b, code, A.device)
-    with torch.cuda.device(A.device):
-        _lib.check(_lib.load().b2mm_gemm(
-            A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, A.stride(1), B.stride(1), out.stride(1),
-            b, A.stride(0), B.stride(0), out.stride(0), code,
-            ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr()))
+    _call_gemm(A, B, out, M, N, K, A.stride(1), B.stride(1), out.stride(1), b, A.stride(0), B.stride(0), out.stride(0), code)
     return out
 
 

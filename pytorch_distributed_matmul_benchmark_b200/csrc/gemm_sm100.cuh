@@ -264,6 +264,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // Let the next kernel in the stream be scheduled onto SMs as this grid drains (it waits below, after its
+  // own prologue, until this grid has completed).  Only has an effect when that kernel asks for it at launch.
+  if (threadIdx.x == 0) griddep_launch_dependents();
   const uint32_t cta_rank = (G == 1) ? 0u : cluster_ctarank();
   const int cluster_id = blockIdx.x / G;
   const int num_clusters = gridDim.x / G;
@@ -305,6 +308,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if constexpr (G == 2) cluster_sync(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_addr));
+  // Everything above touched only this CTA's own shared memory / TMEM; from here on global memory is read and
+  // written, so wait for the preceding grid (a no-op unless launched with programmatic serialization).
+  griddep_wait();
 
   // ---- tile sequence -------------------------------------------------------
   // Every role walks the same sequence of tiles: its cluster's own index first, then either

@@ -312,5 +312,11 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
                : "memory");
 }
 
+// Programmatic dependent launch (the kernel after this one in the stream may be scheduled before this
+// one has finished; it blocks in griddep_wait until this grid has completed and its writes are visible).
+// Both are no-ops for a kernel launched without the programmatic-serialization attribute.
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 }  // namespace ptx
 }  // namespace b2mm

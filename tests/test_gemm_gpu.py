@@ -238,3 +238,30 @@ def test_host_gemm_pipelined_transfers_match_device_path():
     assert rel_err(hC, oracle.gemm_block_f64(hA, hB, 0, M, 0, N)) <= TOL[torch.bfloat16]
     with pytest.raises(RuntimeError, match="pinned"):
         g(torch.zeros(M, K, dtype=torch.bfloat16), hB, hC)
+
+
+def test_programmatic_dependent_launch_keeps_dependencies(monkeypatch):
+    """GEMMs are launched so that the next one may become resident while the previous one drains (PDL).  A chain in
+    which each GEMM reads the previous one's output, and write-after-write on one C, must give the bits that
+    serialised launches (B2MM_PDL=0) give."""
+    results = {}
+    for pdl in ("0", "1"):
+        monkeypatch.setenv("B2MM_PDL", pdl)
+        for N, dt in ((1024, torch.bfloat16), (768, torch.float32)):
+            torch.manual_seed(N)
+            X = torch.randn(N, N, dtype=dt, device=DEV)
+            W = torch.randn(N, N, dtype=dt, device=DEV) / N ** 0.5
+            bufs = [torch.empty(N, N, dtype=dt, device=DEV) for _ in range(2)]
+            cur = X
+            for i in range(16):
+                b2.matmul(cur, W, out=bufs[i % 2])
+                cur = bufs[i % 2]
+            C = torch.empty(N, N, dtype=dt, device=DEV)
+            for i in range(16):
+                b2.matmul(X if i % 2 else W, W, out=C)
+            torch.cuda.synchronize()
+            results[(pdl, N)] = (cur.clone(), C.clone())
+    for N in (1024, 768):
+        assert torch.equal(results[("0", N)][0], results[("1", N)][0])
+        assert torch.equal(results[("0", N)][1], results[("1", N)][1])
+        assert torch.isfinite(results[("1", N)][0]).all()

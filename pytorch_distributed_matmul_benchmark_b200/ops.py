@@ -156,14 +156,19 @@ class HostGemm:
         self.M, self.N, self.K, self.dtype, self.panels = M, N, K, dtype, panels
         self.device = torch.device(device)
         self.dA = torch.empty(M, K, dtype=dtype, device=self.device)
-        self.dB = torch.empty(K, N, dtype=dtype, device=self.device)
+        # B is read by every panel's GEMM, so it is double buffered: the next call's B goes up while this call's
+        # GEMMs are still running.  A and C are reused panel by panel (per-panel events below).
+        self.dB = [torch.empty(K, N, dtype=dtype, device=self.device) for _ in range(2)]
         self.dC = torch.empty(M, N, dtype=dtype, device=self.device)
         self.up = torch.cuda.Stream(device=self.device)
         self.down = torch.cuda.Stream(device=self.device)
         self.ev_b = torch.cuda.Event()
         self.ev_a = [torch.cuda.Event() for _ in range(panels)]
-        self.ev_c = [torch.cuda.Event() for _ in range(panels)]
+        self.ev_c = [torch.cuda.Event() for _ in range(panels)]  # GEMM of panel i finished (dA[i], dB read; dC[i] written)
+        self.ev_d = [torch.cuda.Event() for _ in range(panels)]  # C panel i has left the device
+        self.ev_b_free = [torch.cuda.Event(), torch.cuda.Event()]  # last GEMM that read dB[j] finished
         self.ev_done = torch.cuda.Event()
+        self.calls = 0
 
     def __call__(self, hA: torch.Tensor, hB: torch.Tensor, hC: torch.Tensor) -> torch.Tensor:
         for t in (hA, hB, hC):
@@ -171,26 +176,37 @@ class HostGemm:
                 raise RuntimeError("HostGemm takes pinned host tensors")
         main = torch.cuda.current_stream(self.device)
         rows = self.M // self.panels
-        # dA / dB may be refilled as soon as the previous call's last GEMM has read them; its C may still be on
-        # its way down (the copy engines are independent), so back-to-back calls overlap by that tail
-        self.up.wait_event(self.ev_c[-1])
+        first = self.calls == 0
+        dB = self.dB[self.calls % 2]
         self.down.wait_stream(main)
+        # Back-to-back calls overlap: the upload stream never waits for the previous call as a whole, only for the
+        # GEMM that last read the buffer it is about to overwrite (recorded two calls ago for dB, one call ago per
+        # A panel), so in steady state the host->device link stays busy and a call costs one upload of A and B.
         with torch.cuda.stream(self.up):
-            self.dB.copy_(hB, non_blocking=True)
+            if self.calls >= 2:
+                self.up.wait_event(self.ev_b_free[self.calls % 2])
+            dB.copy_(hB, non_blocking=True)
             self.ev_b.record()
             for i in range(self.panels):
+                if not first:
+                    self.up.wait_event(self.ev_c[i])
                 self.dA[i * rows:(i + 1) * rows].copy_(hA[i * rows:(i + 1) * rows], non_blocking=True)
                 self.ev_a[i].record()
         main.wait_event(self.ev_b)
         for i in range(self.panels):
             main.wait_event(self.ev_a[i])
-            matmul(self.dA[i * rows:(i + 1) * rows], self.dB, out=self.dC[i * rows:(i + 1) * rows])
+            if not first:
+                main.wait_event(self.ev_d[i])  # the previous call's C panel has been copied out of dC[i]
+            matmul(self.dA[i * rows:(i + 1) * rows], dB, out=self.dC[i * rows:(i + 1) * rows])
             self.ev_c[i].record(main)
             with torch.cuda.stream(self.down):
                 self.down.wait_event(self.ev_c[i])
                 hC[i * rows:(i + 1) * rows].copy_(self.dC[i * rows:(i + 1) * rows], non_blocking=True)
+                self.ev_d[i].record()
+        self.ev_b_free[self.calls % 2].record(main)
         self.ev_done.record(self.down)
         main.wait_event(self.ev_done)  # on the caller's stream, the call is complete when hC is
+        self.calls += 1
         return hC
 
 

@@ -238,6 +238,18 @@ def test_host_gemm_pipelined_transfers_match_device_path():
     assert rel_err(hC, oracle.gemm_block_f64(hA, hB, 0, M, 0, N)) <= TOL[torch.bfloat16]
     with pytest.raises(RuntimeError, match="pinned"):
         g(torch.zeros(M, K, dtype=torch.bfloat16), hB, hC)
+    # back-to-back calls with different operands and no synchronisation in between: the calls overlap (the next
+    # upload starts while the previous GEMMs / downloads are in flight), every result must still be its own
+    sets = []
+    for k in range(5):
+        a = torch.randn(M, K, dtype=torch.bfloat16).pin_memory()
+        b = torch.randn(K, N, dtype=torch.bfloat16).pin_memory()
+        sets.append((a, b, torch.zeros(M, N, dtype=torch.bfloat16).pin_memory()))
+    for a, b, c in sets:
+        g(a, b, c)
+    torch.cuda.synchronize()
+    for a, b, c in sets:
+        assert torch.equal(c, b2.matmul(a.to(DEV), b.to(DEV)).cpu())
 
 
 def test_programmatic_dependent_launch_keeps_dependencies(monkeypatch):

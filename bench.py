@@ -121,9 +121,15 @@ def cpu_reference_arm(steps: int, warmup: int, budget_s: float = 150.0) -> dict:
     dt = (time.perf_counter() - t0) / max(steps, 1)
     tflops = 2.0 * m * N * N / dt / 1e12
     assert abs(reference_port.calculate_tflops(N, dt * N / m) - tflops) < 1e-9 * max(tflops, 1)
+    del A, B, slab
+    # BASELINE.json configs[0], the reference's own CPU-runnable case: 4096^3 float32, benchmark_matmul's CPU branch
+    c1_time, c1_tflops = reference_port.benchmark_matmul_cpu(4096, torch.float32, num_iterations=5, warmup_iterations=1, seed=0)
+    config1 = {"workload": "4096x4096x4096 float32, torch.matmul on CPU (BASELINE.json configs[0]), 1 warm-up + 5 timed",
+               "value": c1_tflops, "unit": UNIT, "ms": c1_time * 1000, "cores": cores}
     return {"value": tflops, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"rows [0,{m}) of the {N}^3 bf16 product per step ({m / N:.4f} of a step), torch.matmul on CPU, "
-                      f"{warmup} warm-up + {steps} timed", "ms_per_step": dt * 1000 * N / m, "host_cpus": os.cpu_count()}
+                      f"{warmup} warm-up + {steps} timed", "ms_per_step": dt * 1000 * N / m, "host_cpus": os.cpu_count(),
+            "config1": config1}
 
 
 def run_reference(args) -> None:
@@ -136,7 +142,7 @@ def run_reference(args) -> None:
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"{N}x{N}x{N} bfloat16 GEMM, reference CPU path (torch.matmul, matmul_benchmark.py:69-74)",
                        "sizes": [N], "mode": "independent"},
-            "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "config1")},
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -258,7 +264,7 @@ def run_b2mm(args) -> None:
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         c = cpu_reference_arm(steps=3, warmup=1, budget_s=20.0)
-        cpu = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cpu = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample", "config1")}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",

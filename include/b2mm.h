@@ -256,6 +256,23 @@ B2MM_API int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B,
                                        size_t workspace_bytes, b2mm_stream_t compute, b2mm_stream_t comm_stream);
 
 /*
+ * The two calls above with the reduction done INSIDE the NVSwitch (NVLS): `multicast_buf` / `C_multicast` is a
+ * multicast address (cuMulticastCreate / cuMulticastBindMem, mapped by the caller) bound to the same buffer
+ * on every rank; each rank issues multimem.ld_reduce (sum over all ranks, fp32 accumulation in the switch, one
+ * rounding) and multimem.st (result into every rank's buffer) for its 1/world slice.  Half the NVLink traffic
+ * of pull/add/push at world = 8 and no arithmetic on the SMs.  Synchronisation (signal pads, band counters) and
+ * completion semantics are those of b2mm_all_reduce_p2p_sync / b2mm_gemm_allreduce_fused; C_local is this rank's
+ * ordinary (unicast) mapping of the same memory, which the GEMM writes.  Stands where dist.all_reduce(C, op=SUM)
+ * (matmul_scaling_benchmark.py:125,150) lets NCCL pick its NVLS algorithm.
+ */
+B2MM_API int b2mm_all_reduce_nvls_sync(void* comm, void* multicast_buf, void* const* peer_signals, int64_t count, int dtype,
+                                       b2mm_stream_t stream);
+B2MM_API int b2mm_gemm_allreduce_nvls(void* comm, const void* A, const void* B, void* C_local, void* C_multicast,
+                                      void* const* peer_signals, int* band_counters, int64_t N, int64_t local_batch,
+                                      int dtype, int n_bands, void* workspace, size_t workspace_bytes,
+                                      b2mm_stream_t compute, b2mm_stream_t comm_stream);
+
+/*
  * matrix_parallel with the gather pipelined behind compute
  * (after backup/matmul_overlap_benchmark.py:93-180, made race-free):
  * C_local = A * B_local is computed in `n_panels` row panels on `compute`;

@@ -53,6 +53,9 @@ SIGNATURES = {
                                         c_int, c_void_p, c_size_t, c_void_p, c_void_p]),
     "b2mm_gemm_allreduce_fused": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p),
                                           c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "b2mm_all_reduce_nvls_sync": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int64, c_int, c_void_p]),
+    "b2mm_gemm_allreduce_nvls": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_void_p,
+                                         c_int64, c_int64, c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p]),
     "b2mm_gemm_allgather_overlap": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64,
                                             c_int64, c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p]),
     "b2mm_gemm_allreduce_overlap": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_int,

@@ -144,13 +144,10 @@ __device__ __forceinline__ void wait_epoch(const int* addr, int epoch) {
   }
 }
 
-// Needs no shared memory and few registers on purpose: its CTAs are meant to be co-resident with the
-// GEMM's (which own all of an SM's shared memory but few of its threads), so the reduction of panel i
-// runs on the same SMs as the GEMM of panel i+1 and nothing has to be reserved for it.
-template <typename T, int kUnroll>
-__global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(PeerPtrs ptrs, SignalPtrs sig, int rank, int world, int epoch,
-                                                                  int64_t vec_begin, int64_t vec_count,
-                                                                  const int* band_counter, int band_target) {
+// Common start of the self-synchronising reductions: wait (on the device) for the local GEMM to have
+// published this row band, tell every rank, wait for every rank.
+__device__ __forceinline__ void sync_reduce_prologue(const SignalPtrs& sig, int rank, int world, int epoch,
+                                                     const int* band_counter, int band_target) {
   if (band_counter != nullptr && threadIdx.x == 0) {
     // Launched next to the GEMM that produces the data: wait until the GEMM's epilogues have published
     // this row band (GemmParams::band_counter) before telling the other ranks that it is ready.
@@ -170,6 +167,16 @@ __global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(PeerPtrs ptrs, 
     wait_epoch(sig.p[rank] + threadIdx.x, epoch);                           // ... and so is everybody else's
   }
   __syncthreads();
+}
+
+// Needs no shared memory and few registers on purpose: its CTAs are meant to be co-resident with the
+// GEMM's (which own all of an SM's shared memory but few of its threads), so the reduction of panel i
+// runs on the same SMs as the GEMM of panel i+1 and nothing has to be reserved for it.
+template <typename T, int kUnroll>
+__global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(PeerPtrs ptrs, SignalPtrs sig, int rank, int world, int epoch,
+                                                                  int64_t vec_begin, int64_t vec_count,
+                                                                  const int* band_counter, int band_target) {
+  sync_reduce_prologue(sig, rank, world, epoch, band_counter, band_target);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   constexpr int kLanes = sizeof(T) == 4 ? 4 : 8;
   for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < vec_count; base += stride * kUnroll) {
@@ -221,6 +228,61 @@ __global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(PeerPtrs ptrs, 
           asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(out.x), "r"(out.y), "r"(out.z), "r"(out.w) : "memory");
         }
       }
+    }
+  }
+}
+
+// ---- the same, reduced INSIDE the NVSwitch (NVLS) ---------------------------------------------
+// `mc` is a multicast address bound to every rank's buffer.  multimem.ld_reduce returns the sum over all
+// ranks of one 16-byte vector (added in the switch, fp32 accumulation, one rounding); multimem.st writes the
+// result into every rank's buffer.  Per GPU and direction 1 x the buffer crosses NVLink instead of
+// 2 x (world-1)/world x world/... of the pull/push kernel above (half the traffic at world = 8), and the
+// SMs do no arithmetic at all: they only issue the requests.
+template <typename T>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add(const uint4* mc);
+template <>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add<__nv_bfloat16>(const uint4* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+template <>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add<__half>(const uint4* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+template <>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add<float>(const uint4* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(uint4* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <typename T, int kUnroll>
+__global__ void __launch_bounds__(256) allreduce_nvls_sync_kernel(void* mc, SignalPtrs sig, int rank, int world, int epoch,
+                                                                   int64_t vec_begin, int64_t vec_count,
+                                                                   const int* band_counter, int band_target) {
+  sync_reduce_prologue(sig, rank, world, epoch, band_counter, band_target);
+  uint4* slice = reinterpret_cast<uint4*>(mc) + vec_begin;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < vec_count; base += stride * kUnroll) {
+    uint4 v[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + u * stride;
+      if (i < vec_count) v[u] = multimem_ld_reduce_add<T>(slice + i);
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + u * stride;
+      if (i < vec_count) multimem_st(slice + i, v[u]);
     }
   }
 }

@@ -398,14 +398,23 @@ static void prefer_gemm_carveout() {
     cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__nv_bfloat16, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__half, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(allreduce_p2p_sync_kernel<float, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__nv_bfloat16, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__nv_bfloat16, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__half, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<float, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(p2p_done_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, co);
   });
+}
+
+static bool env_unroll8() {
+  const char* v = getenv("B2MM_NVLS_UNROLL");
+  return v && atoi(v) == 8;
 }
 
 // One self-synchronising reduction launch (see allreduce_p2p.cuh) over this rank's slice of
 // [elem_off, elem_off + count); band_counter may be null.
 static int launch_sync_reduce(Comm* c, const PeerPtrs& pp, const SignalPtrs& sp, int64_t elem_off, int64_t count, int dtype,
-                              const int* band_counter, int band_target, cudaStream_t cs) {
+                              const int* band_counter, int band_target, cudaStream_t cs, void* mc = nullptr) {
   const int es = dtype_bytes(dtype);
   const int64_t vecs = count * es / 16, per = vecs / c->world;
   const int64_t begin = elem_off * es / 16 + per * c->rank;
@@ -416,6 +425,24 @@ static int launch_sync_reduce(Comm* c, const PeerPtrs& pp, const SignalPtrs& sp,
   int ctas = (v && *v) ? atoi(v) : device_sm_count() - 8;
   if (ctas < 1) ctas = 1;
   const int epoch = ++c->ready_epoch;
+  if (mc) {  // reduced inside the NVSwitch through the multicast mapping of the buffers
+    if (dtype == B2MM_BF16 && env_unroll8()) {  // experiment: more requests in flight per thread
+      allreduce_nvls_sync_kernel<__nv_bfloat16, 8><<<ctas, 256, 0, cs>>>(mc, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target);
+      cudaError_t e8 = cudaGetLastError();
+      if (e8 != cudaSuccess) return fail(B2MM_ERR_CUDA, "NVLS all_reduce launch failed: %s", cudaGetErrorString(e8));
+      count_launch(1);
+      return B2MM_OK;
+    }
+    switch (dtype) {
+      case B2MM_BF16: allreduce_nvls_sync_kernel<__nv_bfloat16, kSyncUnroll><<<ctas, 256, 0, cs>>>(mc, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
+      case B2MM_FP16: allreduce_nvls_sync_kernel<__half, kSyncUnroll><<<ctas, 256, 0, cs>>>(mc, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
+      default: allreduce_nvls_sync_kernel<float, kSyncUnroll><<<ctas, 256, 0, cs>>>(mc, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "NVLS all_reduce launch failed: %s", cudaGetErrorString(e));
+    count_launch(1);
+    return B2MM_OK;
+  }
   switch (dtype) {
     case B2MM_BF16: allreduce_p2p_sync_kernel<__nv_bfloat16, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
     case B2MM_FP16: allreduce_p2p_sync_kernel<__half, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
@@ -453,11 +480,56 @@ int b2mm_all_reduce_p2p_sync(void* comm, void* const* peer_bufs, void* const* pe
   return launch_done(c, sp, (cudaStream_t)stream);
 }
 
+int b2mm_all_reduce_nvls_sync(void* comm, void* multicast_buf, void* const* peer_signals, int64_t count, int dtype,
+                              b2mm_stream_t stream) {
+  Comm* c = (Comm*)comm;
+  if (!c || !multicast_buf || !peer_signals || count < 0 || !dtype_bytes(dtype) || c->world > 8)
+    return fail(B2MM_ERR_BAD_ARG, "bad NVLS all_reduce argument");
+  if (count == 0) return B2MM_OK;
+  if ((count * dtype_bytes(dtype)) % 16 || ((uintptr_t)multicast_buf & 15))
+    return fail(B2MM_ERR_UNSUPPORTED, "NVLS all_reduce needs a 16-byte aligned buffer of a multiple of 16 bytes");
+  PeerPtrs pp;
+  SignalPtrs sp;
+  for (int d = 0; d < 8; ++d) {
+    pp.p[d] = nullptr;
+    sp.p[d] = (int*)peer_signals[d < c->world ? d : 0];
+  }
+  prefer_gemm_carveout();
+  int rc;
+  if ((rc = launch_sync_reduce(c, pp, sp, 0, count, dtype, nullptr, 0, (cudaStream_t)stream, multicast_buf))) return rc;
+  return launch_done(c, sp, (cudaStream_t)stream);
+}
+
+static int gemm_allreduce_fused_impl(Comm* c, const void* A, const void* B, void* C_local, void* const* peer_C, void* mc,
+                                     void* const* peer_signals, int* band_counters, int64_t N, int64_t local_batch,
+                                     int dtype, int n_bands, void* workspace, size_t workspace_bytes,
+                                     b2mm_stream_t compute_, b2mm_stream_t comm_stream_);
+
 int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* const* peer_C, void* const* peer_signals,
                               int* band_counters, int64_t N, int64_t local_batch, int dtype, int n_bands, void* workspace,
                               size_t workspace_bytes, b2mm_stream_t compute_, b2mm_stream_t comm_stream_) {
   Comm* c = (Comm*)comm;
-  if (!c || !peer_C || !peer_signals || !band_counters || !dtype_bytes(dtype) || c->world > 8)
+  if (!c || !peer_C) return fail(B2MM_ERR_BAD_ARG, "bad comm, dtype or buffer list");
+  return gemm_allreduce_fused_impl(c, A, B, peer_C[c->rank], peer_C, nullptr, peer_signals, band_counters, N, local_batch, dtype,
+                                   n_bands, workspace, workspace_bytes, compute_, comm_stream_);
+}
+
+int b2mm_gemm_allreduce_nvls(void* comm, const void* A, const void* B, void* C_local, void* C_multicast,
+                             void* const* peer_signals, int* band_counters, int64_t N, int64_t local_batch, int dtype,
+                             int n_bands, void* workspace, size_t workspace_bytes, b2mm_stream_t compute_,
+                             b2mm_stream_t comm_stream_) {
+  Comm* c = (Comm*)comm;
+  if (!c || !C_local || !C_multicast) return fail(B2MM_ERR_BAD_ARG, "bad comm or buffer");
+  return gemm_allreduce_fused_impl(c, A, B, C_local, nullptr, C_multicast, peer_signals, band_counters, N, local_batch, dtype,
+                                   n_bands, workspace, workspace_bytes, compute_, comm_stream_);
+}
+
+// One of peer_C (pull / add / push over peer mappings) and mc (reduced in the switch) is non-null.
+static int gemm_allreduce_fused_impl(Comm* c, const void* A, const void* B, void* C_local, void* const* peer_C, void* mc,
+                                     void* const* peer_signals, int* band_counters, int64_t N, int64_t local_batch,
+                                     int dtype, int n_bands, void* workspace, size_t workspace_bytes,
+                                     b2mm_stream_t compute_, b2mm_stream_t comm_stream_) {
+  if (!c || (!peer_C && !mc) || !C_local || !peer_signals || !band_counters || !dtype_bytes(dtype) || c->world > 8)
     return fail(B2MM_ERR_BAD_ARG, "bad comm, dtype or buffer list");
   if (local_batch == 0) return B2MM_OK;
   if (n_bands < 1 || n_bands * local_batch > kMaxPanels)
@@ -470,7 +542,7 @@ int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* co
   PeerPtrs pp;
   SignalPtrs sp;
   for (int d = 0; d < 8; ++d) {
-    pp.p[d] = peer_C[d < c->world ? d : 0];
+    pp.p[d] = peer_C ? peer_C[d < c->world ? d : 0] : nullptr;
     sp.p[d] = (int*)peer_signals[d < c->world ? d : 0];
   }
   prefer_gemm_carveout();
@@ -483,7 +555,7 @@ int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* co
   GemmOpts opts;
   opts.band_counter = band_counters;
   opts.band_rows = (int)band_rows;
-  int rc = gemm_impl(A, B, peer_C[c->rank], N, N, N, N, N, N, local_batch, N * N, N * N, N * N, dtype, workspace, workspace_bytes,
+  int rc = gemm_impl(A, B, C_local, N, N, N, N, N, N, local_batch, N * N, N * N, N * N, dtype, workspace, workspace_bytes,
                      compute, opts);
   if (rc) return rc;
   if (opts.bands_per_batch != n_bands) return fail(B2MM_ERR_UNSUPPORTED, "band geometry mismatch (%d vs %d)", opts.bands_per_batch, n_bands);
@@ -492,7 +564,7 @@ int b2mm_gemm_allreduce_fused(void* comm, const void* A, const void* B, void* co
     for (int i = 0; i < n_bands; ++i) {
       const int64_t elem_off = b * N * N + (int64_t)i * band_rows * N;
       if ((rc = launch_sync_reduce(c, pp, sp, elem_off, band_rows * N, dtype, band_counters + b * n_bands + i,
-                                   opts.signals_per_band, cs)))
+                                   opts.signals_per_band, cs, mc)))
         return rc;
     }
   }

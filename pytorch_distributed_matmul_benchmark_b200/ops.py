@@ -254,6 +254,7 @@ class Communicator:
                                           ctypes.byref(self._comm)))
         self.comm_stream = torch.cuda.Stream(device=device, priority=-1)
         self._shared: List[SharedSlabs] = []
+        self._multicast: list = []
         self._signals: Optional[SharedSlabs] = None
 
     def release_shared(self) -> None:
@@ -270,6 +271,9 @@ class Communicator:
         if dist.is_initialized():  # unconditional: ranks may disagree on whether anything was shared after an error
             dist.barrier()
         self._shared = []
+        for mc in self._multicast:  # collective as well (every rank made the same buffers in the same order)
+            mc.close()
+        self._multicast = []
 
     def destroy(self) -> None:
         if self._comm:
@@ -347,6 +351,21 @@ class Communicator:
         """A buffer shaped like `t` on every rank, each visible to every other rank (for the p2p all_reduce)."""
         return self.share(torch.empty_like(t))
 
+    def multicast_like(self, t: torch.Tensor):
+        """A buffer shaped like `t` on every rank, all bound to one NVSwitch multicast object (NVLS): `.local` is this
+        rank's tensor, `.mc_ptr` the address through which the switch reduces / broadcasts.  Collective."""
+        from .multicast import MulticastBuffer
+        buf = MulticastBuffer(self.rank, self.world_size, self.device, tuple(t.shape), t.dtype)
+        self._multicast.append(buf)
+        return buf
+
+    def all_reduce_nvls(self, buf, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """In-place SUM of buf.local over ranks, reduced inside the NVSwitch (multimem.ld_reduce / multimem.st)."""
+        t = buf.local
+        _lib.check(_lib.load().b2mm_all_reduce_nvls_sync(self._comm, buf.mc_ptr, self._signal_pads().peer_ptrs, t.numel(),
+                                                         _dtype_code(t), _stream_ptr(stream)))
+        return t
+
     def all_reduce_p2p(self, shared: "SharedSlabs") -> torch.Tensor:
         """In-place SUM of shared.local over ranks by the library's own NVLink kernel (fp32 adds, one rounding)."""
         t = shared.local
@@ -389,6 +408,12 @@ class Communicator:
         code = _dtype_code(A)
         ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)
         self.comm_stream.wait_stream(torch.cuda.current_stream())
+        if hasattr(shared_C, "mc_ptr"):  # MulticastBuffer: the bands are reduced inside the NVSwitch
+            _lib.check(_lib.load().b2mm_gemm_allreduce_nvls(
+                self._comm, A.data_ptr(), B.data_ptr(), shared_C.local.data_ptr(), shared_C.mc_ptr, self._signals.peer_ptrs,
+                self._band_counters.data_ptr(), N, b, code, n_panels,
+                ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr(), self.comm_stream.cuda_stream))
+            return shared_C.local
         _lib.check(_lib.load().b2mm_gemm_allreduce_fused(
             self._comm, A.data_ptr(), B.data_ptr(), shared_C.peer_ptrs, self._signals.peer_ptrs,
             self._band_counters.data_ptr(), N, b, code, n_panels,

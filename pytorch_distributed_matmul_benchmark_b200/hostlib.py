@@ -99,6 +99,8 @@ class Ops:
     shared_slabs: Optional[Callable] = None  # (M, n_local, dtype) -> SharedSlabs
     matmul_allgather_fused: Optional[Callable] = None  # (A, B_local, shared) -> slabs
     shared_like: Optional[Callable] = None  # (t) -> SharedSlabs
+    reduce_buffer_like: Optional[Callable] = None  # (t) -> MulticastBuffer (NVLS) or SharedSlabs; has .local
+    nvls_available: Callable = lambda: False
     bmm_allreduce_fused: Optional[Callable] = None  # (A, B, shared_C, n_panels) -> C
     all_reduce_sync: Optional[Callable] = None  # (shared, stream=None) -> t; peer-memory all_reduce, co-resident with a GEMM
     release_shared: Callable = lambda: None  # collective: unmap peer buffers before their owners free them
@@ -125,6 +127,8 @@ def device_ops(rank: int, world_size: int, device: str) -> Ops:
         shared_slabs=comm.shared_slabs if comm else None,
         matmul_allgather_fused=comm.matmul_allgather_fused if comm else None,
         shared_like=comm.shared_like if comm else None,
+        reduce_buffer_like=comm.reduce_buffer_like if comm else None,
+        nvls_available=comm.nvls_available if comm else (lambda: False),
         bmm_allreduce_fused=comm.bmm_allreduce_fused if comm else None,
         all_reduce_sync=comm.all_reduce_sync if comm else None,
         release_shared=comm.release_shared if comm else (lambda: None),

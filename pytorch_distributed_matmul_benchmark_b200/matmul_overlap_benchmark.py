@@ -6,7 +6,9 @@ is underneath, and the races are gone:
 
 * the GEMM is libb2mm.so's tcgen05 kernel;
 * `no_overlap` reduces with the library's NCCL all_reduce, serialised exactly like :51-69;
-* `overlap` / `pipeline` reduce with the library's own peer-memory all_reduce (b2mm_all_reduce_p2p_sync), whose
+* `overlap` / `pipeline` reduce with the library's own self-synchronising all_reduce — inside the NVSwitch
+  (b2mm_all_reduce_nvls_sync: multimem.ld_reduce / multimem.st on multicast buffers) where the hardware has it,
+  else pull / add / push over peer mappings (b2mm_all_reduce_p2p_sync) — whose
   CTAs are co-resident with the GEMM's: the reduction of C_i runs on a second stream while GEMM i+1 runs on
   the whole device.  Every edge is an event: the reduction waits for its GEMM (the reference never makes
   comm_stream wait for compute_stream, :131-137), and a buffer is rewritten only after its reduction has
@@ -100,7 +102,9 @@ def _check_reduced_product(ops: hostlib.Ops, reduce_fn, out: torch.Tensor, matri
     ops.synchronize()
     rms = want.pow(2).mean().sqrt()
     err = ((out.double() - want).abs() / (want.abs() + rms)).max().item()
-    tol = hostlib.CHECK_TOL[dtype] * max(world - 1, 1)
+    # one rounding per pairwise add for NCCL's ring (world - 1 of them); the NVSwitch adds in fp32 and rounds once,
+    # but (measured) not always to nearest, so its single rounding is allowed a full ulp
+    tol = hostlib.CHECK_TOL[dtype] * max(world - 1, 2)
     if rank == 0:
         print(f"  Parity of the reduced product vs float64 sum: max err {err:.3e} (tolerance {tol:.1e}) -> {'OK' if err <= tol else 'FAIL'}")
     if err > tol:
@@ -114,7 +118,7 @@ def _ring_benchmark(depth: int, matrix_size: int, dtype: torch.dtype, device: st
     Bs = [torch.randn(matrix_size, matrix_size, dtype=dtype, device=device) for _ in range(depth)]
     comm_on = dist.is_initialized() and ops.all_reduce_sync is not None
     if comm_on:
-        Cs = [ops.shared_like(As[0]) for _ in range(depth)]  # peer-visible outputs
+        Cs = [(ops.reduce_buffer_like or ops.shared_like)(As[0]) for _ in range(depth)]  # NVLS or peer-visible outputs
         outs = [c.local for c in Cs]
     else:
         Cs, outs = [None] * depth, [torch.empty_like(As[0]) for _ in range(depth)]

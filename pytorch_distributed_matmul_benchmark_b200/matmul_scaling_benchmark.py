@@ -162,14 +162,15 @@ def benchmark_batch_parallel(matrix_size: int, batch_size: int, dtype: torch.dty
         avg_total_time = avg_overlap
 
     if fused and comm_on and local_batch_size > 0 and ops.bmm_allreduce_fused is not None:
-        shared = ops.shared_like(C)
+        shared = (ops.reduce_buffer_like or ops.shared_like)(C)  # NVLS multicast buffer where available
+        how = "reduced in the NVSwitch" if hasattr(shared, "mc_ptr") else "peer memory"
         for _ in range(min(warmup_iterations, 3)):
             ops.bmm_allreduce_fused(A, B, shared, panels)
         ops.synchronize()
         dist.barrier()
         avg_fused = _timed_loop(ops, lambda: ops.bmm_allreduce_fused(A, B, shared, panels), num_iterations)
         if rank == 0:
-            print(f"    Fused GEMM+all_reduce (peer memory) end-to-end: {avg_fused*1000:.3f} ms ({panels} panels; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
+            print(f"    Fused GEMM+all_reduce ({how}) end-to-end: {avg_fused*1000:.3f} ms ({panels} panels; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
         if check:  # against the NCCL all_reduce of the same product: two roundings of one sum, at most ~1 ulp apart
             ops.bmm(A, B, out=C)
             ops.all_reduce(C)

@@ -359,6 +359,24 @@ class Communicator:
         self._multicast.append(buf)
         return buf
 
+    def nvls_available(self) -> bool:
+        """True when the reductions can be done inside the NVSwitch (multicast objects supported; B2MM_NVLS=0 opts out)."""
+        import os
+        if os.environ.get("B2MM_NVLS", "1") == "0" or self.world_size < 2:
+            return False
+        if getattr(self, "_nvls", None) is None:
+            from .multicast import multicast_supported
+            try:
+                self._nvls = multicast_supported(self.device.index if self.device.index is not None else torch.cuda.current_device())
+            except Exception:  # no cuda-python bindings, or a driver without the attribute
+                self._nvls = False
+        return self._nvls
+
+    def reduce_buffer_like(self, t: torch.Tensor):
+        """The buffer the fused / co-resident all_reduce paths work on: a multicast (NVLS) buffer where the hardware
+        has it, otherwise a peer-mapped one (pull / add / push).  Collective; `.local` is this rank's tensor."""
+        return self.multicast_like(t) if self.nvls_available() else self.shared_like(t)
+
     def all_reduce_nvls(self, buf, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """In-place SUM of buf.local over ranks, reduced inside the NVSwitch (multimem.ld_reduce / multimem.st)."""
         t = buf.local
@@ -394,6 +412,8 @@ class Communicator:
 
     def all_reduce_sync(self, shared: "SharedSlabs", stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """In-place SUM over ranks by the self-synchronising peer-memory kernels (no NCCL); may run beside a GEMM."""
+        if hasattr(shared, "mc_ptr"):
+            return self.all_reduce_nvls(shared, stream)
         t = shared.local
         _lib.check(_lib.load().b2mm_all_reduce_p2p_sync(self._comm, shared.peer_ptrs, self._signal_pads().peer_ptrs, t.numel(),
                                                         _dtype_code(t), _stream_ptr(stream)))

@@ -90,17 +90,37 @@ sharedC = comm.shared_like(C3)
 t_p2p_alone = timed(lambda: comm.all_reduce_p2p(sharedC))
 bp["p2p_allreduce_alone_ms"] = t_p2p_alone
 bp["p2p_allreduce_busbw_GBs"] = bytes_ar * 2 * (ws - 1) / ws / (t_p2p_alone * 1e-3) / 1e9
+mcC = comm.multicast_like(C3) if comm.nvls_available() else None  # reduced inside the NVSwitch
+if mcC is not None:
+    t_nvls_alone = timed(lambda: comm.all_reduce_nvls(mcC))
+    bp["nvls_allreduce_alone_ms"] = t_nvls_alone
+    bp["nvls_allreduce_busbw_GBs"] = bytes_ar * 2 * (ws - 1) / ws / (t_nvls_alone * 1e-3) / 1e9
 rounds = []
-for _ in range(3):
+for _ in range(5):
     tg = timed(lambda: b2.bmm(A3, B3, out=C3), iters=6, warm=2)
     tn = timed(lambda: comm.bmm_allreduce_overlap(A3, B3, C3, 8), iters=6, warm=2)
     tg2 = timed(lambda: b2.bmm(A3, B3, out=C3), iters=6, warm=2)
     tf = timed(lambda: comm.bmm_allreduce_fused(A3, B3, sharedC, 8), iters=6, warm=2)
-    rounds.append({"gemm_only_ms": tg, "nccl_pipelined_ms": tn, "nccl_eff": tg / tn,
-                   "gemm_only_again_ms": tg2, "fused_ms": tf, "fused_eff": tg2 / tf})
+    r = {"gemm_only_ms": tg, "nccl_pipelined_ms": tn, "nccl_eff": tg / tn,
+         "gemm_only_again_ms": tg2, "fused_ms": tf, "fused_eff": tg2 / tf}
+    if mcC is not None:
+        tg3 = timed(lambda: b2.bmm(A3, B3, out=C3), iters=6, warm=2)
+        tv = timed(lambda: comm.bmm_allreduce_fused(A3, B3, mcC, 8), iters=6, warm=2)
+        r.update({"gemm_only_third_ms": tg3, "fused_nvls_ms": tv, "fused_nvls_eff": tg3 / tv})
+    rounds.append(r)
 bp["interleaved_rounds"] = rounds
 bp["nccl_pipelined_weak_eff"] = sum(r["nccl_eff"] for r in rounds) / len(rounds)
 bp["fused_weak_eff"] = sum(r["fused_eff"] for r in rounds) / len(rounds)
+if mcC is not None:
+    effs = sorted(r["fused_nvls_eff"] for r in rounds)
+    bp["fused_nvls_weak_eff"] = sum(effs) / len(effs)
+    bp["fused_nvls_weak_eff_min_median_max"] = [effs[0], effs[len(effs) // 2], effs[-1]]
+    comm.bmm_allreduce_fused(A3, B3, mcC, 8)
+    b2.bmm(A3, B3, out=C3)
+    comm.all_reduce(C3)
+    torch.cuda.synchronize()
+    refn = C3[0, :256].double()
+    bp["fused_nvls_vs_nccl_err"] = max_ranks(((mcC.local[0, :256].double() - refn).abs() / (refn.abs() + refn.pow(2).mean().sqrt())).max().item())
 # parity of the fused path against NCCL's all_reduce of the same product
 comm.bmm_allreduce_fused(A3, B3, sharedC, 8)
 b2.bmm(A3, B3, out=C3)

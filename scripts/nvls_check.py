@@ -75,6 +75,21 @@ try:
         err = max_ranks(rel(buf.local, x))
         res[f"allreduce_{dt}"] = {"const_ok": ok_const, "vs_nccl": err}
         log(f"{dt}: constants {'OK' if ok_const else 'WRONG'}, vs NCCL {err:.3e}")
+    # how does the switch round?  rank 0 holds 1.0, rank 1 holds x * ulp(1.0) (bf16 ulp = 2^-7), the others 0
+    probe = comm.multicast_like(torch.empty(8, dtype=torch.bfloat16, device=dev))
+    fracs = [0.25, 0.5, 0.75, 1.25, 1.5, 1.75, 2.5, 3.5]
+    probe.local.zero_()
+    if rank == 0:
+        probe.local.fill_(1.0)
+    elif rank == 1:
+        probe.local.copy_(torch.tensor([f * 2.0 ** -7 for f in fracs], dtype=torch.bfloat16))
+    torch.cuda.synchronize()
+    dist.barrier()
+    comm.all_reduce_nvls(probe)
+    torch.cuda.synchronize()
+    got = [round((v - 1.0) / 2.0 ** -7, 3) for v in probe.local.float().tolist()]
+    res["rounding_probe"] = {"added_ulps": fracs, "result_ulps_above_one": got}
+    log("rounding probe: 1.0 + x ulp ->", dict(zip(fracs, got)))
     comm.release_shared()
 
     # 2. fused GEMM + NVLS reduction, small, against the float64 sum of the per-rank (rounded) products

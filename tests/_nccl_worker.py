@@ -96,6 +96,37 @@ def main(out_path):
     comm.all_reduce(Cn)
     torch.cuda.synchronize()
     res["fused_allreduce_vs_nccl"] = rel(shC.local, Cn.double()) <= (ws - 1) * TOL[torch.bfloat16]
+    # the same reductions done inside the NVSwitch (multicast buffers), where the box has NVLS
+    res["nvls_available"] = "yes" if comm.nvls_available() else "no"
+    if comm.nvls_available():
+        for dt in (torch.bfloat16, torch.float32):
+            buf = comm.multicast_like(torch.empty(3, 4096, dtype=dt, device=dev))
+            buf.local.fill_(float(rank + 1))
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.all_reduce_nvls(buf)
+            torch.cuda.synchronize()
+            res[f"nvls_constants_{dt}"] = bool(torch.all(buf.local == float(ws * (ws + 1) // 2)))
+            parts = []
+            for r in range(ws):
+                torch.manual_seed(300 + r)
+                parts.append(torch.randn(3, 4096, dtype=dt, device=dev))
+            dist.barrier()  # every rank has read the previous result before anybody overwrites its buffer
+            buf.local.copy_(parts[rank])
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.all_reduce_sync(buf)  # dispatches to the NVLS kernel for a multicast buffer
+            torch.cuda.synchronize()
+            # the switch adds in fp32 and rounds once, but (measured) not always to nearest: allow 1 ulp instead of 1/2
+            res[f"nvls_all_reduce_{dt}"] = rel(buf.local, sum(p.double() for p in parts)) <= 2 * TOL[dt]
+        mcC = comm.multicast_like(torch.empty(2, 1024, 1024, dtype=torch.bfloat16, device=dev))
+        for _ in range(2):
+            comm.bmm_allreduce_fused(Ab, Bb, mcC, 2)
+        torch.cuda.synchronize()
+        res["fused_allreduce_nvls"] = rel(mcC.local, want) <= 2 * TOL[torch.bfloat16]  # sum of the rounded products, 1 ulp
+        res["fused_allreduce_nvls_vs_peer_path"] = rel(mcC.local, shC.local.double()) <= 2 * TOL[torch.bfloat16]
+        comm.release_shared()
+
     # share -> use -> release -> free, more often than the import table is long: mappings are given back (an owner
     # never frees memory a peer still maps) and a freed-and-reallocated block can be shared again
     ok = True

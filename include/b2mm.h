@@ -208,6 +208,16 @@ B2MM_API int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void*
                                        b2mm_stream_t stream);
 
 /*
+ * The same with ONE store per chunk: `slabs_multicast` is the multicast address (see b2mm_all_reduce_nvls_sync) of the
+ * [world][M][n_local] gather buffer every rank allocated; the epilogue's TMA store goes to that address and the
+ * NVSwitch replicates it into all ranks' copies, so a GPU sends each byte of its slab once instead of world - 1 times.
+ * Replaces C_local = torch.matmul(A, B_local) + dist.all_gather (matmul_scaling_benchmark.py:211 + :221), like the call above.
+ */
+B2MM_API int b2mm_gemm_allgather_nvls(const void* A, const void* B_local, void* slabs_multicast, int rank, int world,
+                                      int64_t M, int64_t n_local, int64_t K, int dtype, void* workspace,
+                                      size_t workspace_bytes, b2mm_stream_t stream);
+
+/*
  * In-place SUM over ranks of `count` elements, done by this library's own kernel over peer-mapped
  * buffers instead of NCCL (replaces dist.all_reduce(C, op=SUM), matmul_scaling_benchmark.py:125,150):
  * each rank pulls its 1/world slice from every rank over NVLink, adds in fp32, rounds once, and pushes

@@ -47,6 +47,8 @@ SIGNATURES = {
     "b2mm_comm_barrier": (c_int, [c_void_p, c_void_p]),
     "b2mm_gemm_allgather_fused": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_int, c_int64, c_int64,
                                           c_int64, c_int, c_void_p, c_size_t, c_void_p]),
+    "b2mm_gemm_allgather_nvls": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_int64, c_int64, c_int,
+                                         c_void_p, c_size_t, c_void_p]),
     "b2mm_all_reduce_p2p": (c_int, [c_void_p, ctypes.POINTER(c_void_p), c_int64, c_int, c_void_p]),
     "b2mm_all_reduce_p2p_sync": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p), c_int64, c_int, c_void_p]),
     "b2mm_gemm_allreduce_p2p": (c_int, [c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int64, c_int64, c_int,

@@ -309,6 +309,22 @@ int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void* const* p
                    (cudaStream_t)stream, opts);
 }
 
+int b2mm_gemm_allgather_nvls(const void* A, const void* B_local, void* slabs_multicast, int rank, int world, int64_t M,
+                             int64_t n_local, int64_t K, int dtype, void* workspace, size_t workspace_bytes,
+                             b2mm_stream_t stream) {
+  const int es = dtype_bytes(dtype);
+  if (es == 0) return fail(B2MM_ERR_BAD_ARG, "unknown dtype %d", dtype);
+  if (!slabs_multicast || world < 1 || rank < 0 || rank >= world) return fail(B2MM_ERR_BAD_ARG, "bad rank/world (%d/%d) or null buffer", rank, world);
+  // ONE destination: slab `rank` of the [world][M][n_local] buffer at its multicast address; the switch
+  // replicates every TMA store into all ranks' copies.
+  void* dst[1] = {(char*)slabs_multicast + (size_t)rank * M * n_local * es};
+  GemmOpts opts;
+  opts.fan_ptrs = dst;
+  opts.fanout = 1;
+  return gemm_impl(A, B_local, nullptr, M, n_local, K, K, n_local, n_local, 1, 0, 0, 0, dtype, workspace, workspace_bytes,
+                   (cudaStream_t)stream, opts);
+}
+
 // One rank's part of the peer-memory all-reduce over elements [elem_off, elem_off + count) of the
 // buffers in `peers` (pull, add in fp32, push); the cross-rank ordering is the caller's.
 static int launch_allreduce_p2p(void* const* peers, int rank, int world, int64_t elem_off, int64_t count, int dtype,

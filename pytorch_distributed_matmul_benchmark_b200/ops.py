@@ -449,6 +449,12 @@ class Communicator:
             raise RuntimeError("shared slabs do not match the problem")
         code = _dtype_code(A)
         ws, ws_bytes = workspace_for(M, n_local, K, 1, code, A.device)
+        if hasattr(shared, "mc_ptr"):  # MulticastBuffer: one store per chunk, replicated by the NVSwitch
+            _lib.check(_lib.load().b2mm_gemm_allgather_nvls(
+                A.data_ptr(), B_local.data_ptr(), shared.mc_ptr, self.rank, self.world_size, M, n_local, K, code,
+                ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr()))
+            self.barrier()
+            return shared.local
         _lib.check(_lib.load().b2mm_gemm_allgather_fused(
             A.data_ptr(), B_local.data_ptr(), shared.peer_ptrs, self.rank, self.world_size, M, n_local, K, code,
             ws.data_ptr() if ws is not None else None, ws_bytes, _stream_ptr()))

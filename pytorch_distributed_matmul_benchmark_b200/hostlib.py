@@ -97,6 +97,7 @@ class Ops:
     matmul_allgather_overlap: Optional[Callable] = None  # (A, B_local, C_local, slabs, n_panels)
     bmm_allreduce_overlap: Optional[Callable] = None  # (A, B, C, n_panels)
     shared_slabs: Optional[Callable] = None  # (M, n_local, dtype) -> SharedSlabs
+    gather_buffer: Optional[Callable] = None  # (M, n_local, dtype) -> MulticastBuffer (NVLS) or SharedSlabs
     matmul_allgather_fused: Optional[Callable] = None  # (A, B_local, shared) -> slabs
     shared_like: Optional[Callable] = None  # (t) -> SharedSlabs
     reduce_buffer_like: Optional[Callable] = None  # (t) -> MulticastBuffer (NVLS) or SharedSlabs; has .local
@@ -125,6 +126,7 @@ def device_ops(rank: int, world_size: int, device: str) -> Ops:
         matmul_allgather_overlap=comm.matmul_allgather_overlap if comm else None,
         bmm_allreduce_overlap=comm.bmm_allreduce_overlap if comm else None,
         shared_slabs=comm.shared_slabs if comm else None,
+        gather_buffer=comm.gather_buffer if comm else None,
         matmul_allgather_fused=comm.matmul_allgather_fused if comm else None,
         shared_like=comm.shared_like if comm else None,
         reduce_buffer_like=comm.reduce_buffer_like if comm else None,

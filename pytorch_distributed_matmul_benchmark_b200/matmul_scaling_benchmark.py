@@ -249,7 +249,8 @@ def benchmark_matrix_parallel(matrix_size: int, dtype: torch.dtype, device: str,
         avg_total_time = avg_overlap
 
     if fused and ops.matmul_allgather_fused is not None:
-        shared = ops.shared_slabs(matrix_size, end_col - start_col, dtype)
+        shared = (ops.gather_buffer or ops.shared_slabs)(matrix_size, end_col - start_col, dtype)
+        how = "one multicast TMA store per chunk" if hasattr(shared, "mc_ptr") else "peer TMA stores"
         shared.local.zero_()
         ops.synchronize()
         dist.barrier()
@@ -259,7 +260,7 @@ def benchmark_matrix_parallel(matrix_size: int, dtype: torch.dtype, device: str,
         dist.barrier()
         avg_fused = _timed_loop(ops, lambda: ops.matmul_allgather_fused(A, B_local, shared), num_iterations)
         if rank == 0:
-            print(f"    Fused GEMM+all_gather end-to-end: {avg_fused*1000:.3f} ms (one kernel + barrier; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
+            print(f"    Fused GEMM+all_gather end-to-end: {avg_fused*1000:.3f} ms (one kernel, {how}, + barrier; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
         avg_total_time = avg_fused
         slabs = shared.local
 

@@ -347,6 +347,13 @@ class Communicator:
         """A [world][M][n_local] gather buffer on every rank, each visible to every other rank."""
         return self.share(torch.empty((self.world_size, M, n_local), dtype=dtype, device=self.device))
 
+    def gather_buffer(self, M: int, n_local: int, dtype: torch.dtype):
+        """The [world][M][n_local] buffer of the fused matrix_parallel path: multicast (one TMA store per chunk, replicated
+        by the NVSwitch) where the hardware has it, else peer-mapped (one store per destination).  Collective."""
+        if self.nvls_available():
+            return self.multicast_like(torch.empty((self.world_size, M, n_local), dtype=dtype, device="meta"))
+        return self.shared_slabs(M, n_local, dtype)
+
     def shared_like(self, t: torch.Tensor) -> "SharedSlabs":
         """A buffer shaped like `t` on every rank, each visible to every other rank (for the p2p all_reduce)."""
         return self.share(torch.empty_like(t))

@@ -119,6 +119,12 @@ def main(out_path):
             torch.cuda.synchronize()
             # the switch adds in fp32 and rounds once, but (measured) not always to nearest: allow 1 ulp instead of 1/2
             res[f"nvls_all_reduce_{dt}"] = rel(buf.local, sum(p.double() for p in parts)) <= 2 * TOL[dt]
+        mcS = comm.gather_buffer(N, e - s, torch.bfloat16)  # matrix_parallel: one multicast TMA store per chunk
+        res["gather_buffer_is_multicast"] = hasattr(mcS, "mc_ptr")
+        for _ in range(2):
+            comm.matmul_allgather_fused(A, B_local, mcS)
+        torch.cuda.synchronize()
+        res["fused_allgather_nvls_equals_nccl_path"] = torch.equal(slabs, mcS.local)
         mcC = comm.multicast_like(torch.empty(2, 1024, 1024, dtype=torch.bfloat16, device=dev))
         for _ in range(2):
             comm.bmm_allreduce_fused(Ab, Bb, mcC, 2)

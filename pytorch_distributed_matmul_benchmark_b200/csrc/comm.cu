@@ -415,16 +415,10 @@ static void prefer_gemm_carveout() {
     cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__half, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(allreduce_p2p_sync_kernel<float, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__nv_bfloat16, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__nv_bfloat16, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__half, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(allreduce_nvls_sync_kernel<float, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
     cudaFuncSetAttribute(p2p_done_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, co);
   });
-}
-
-static bool env_unroll8() {
-  const char* v = getenv("B2MM_NVLS_UNROLL");
-  return v && atoi(v) == 8;
 }
 
 // One self-synchronising reduction launch (see allreduce_p2p.cuh) over this rank's slice of
@@ -444,13 +438,6 @@ static int launch_sync_reduce(Comm* c, const PeerPtrs& pp, const SignalPtrs& sp,
   if (ctas < 1) ctas = 1;
   const int epoch = ++c->ready_epoch;
   if (mc) {  // reduced inside the NVSwitch through the multicast mapping of the buffers
-    if (dtype == B2MM_BF16 && env_unroll8()) {  // experiment: more requests in flight per thread
-      allreduce_nvls_sync_kernel<__nv_bfloat16, 8><<<ctas, 256, 0, cs>>>(mc, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target);
-      cudaError_t e8 = cudaGetLastError();
-      if (e8 != cudaSuccess) return fail(B2MM_ERR_CUDA, "NVLS all_reduce launch failed: %s", cudaGetErrorString(e8));
-      count_launch(1);
-      return B2MM_OK;
-    }
     switch (dtype) {
       case B2MM_BF16: allreduce_nvls_sync_kernel<__nv_bfloat16, kSyncUnroll><<<ctas, 256, 0, cs>>>(mc, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
       case B2MM_FP16: allreduce_nvls_sync_kernel<__half, kSyncUnroll><<<ctas, 256, 0, cs>>>(mc, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;

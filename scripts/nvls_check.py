@@ -125,9 +125,6 @@ try:
     t["nccl_allreduce_ms"] = timed(lambda: comm.all_reduce(C))
     t["p2p_sync_allreduce_ms"] = timed(lambda: comm.all_reduce_sync(p2pC))
     t["nvls_allreduce_ms"] = timed(lambda: comm.all_reduce_nvls(mcC))
-    os.environ["B2MM_NVLS_UNROLL"] = "8"
-    t["nvls_unroll8_allreduce_ms"] = timed(lambda: comm.all_reduce_nvls(mcC))
-    os.environ.pop("B2MM_NVLS_UNROLL")
     for ctas in ("32", "64"):
         os.environ["B2MM_P2P_CTAS"] = ctas
         t[f"nvls_allreduce_{ctas}ctas_ms"] = timed(lambda: comm.all_reduce_nvls(mcC))

@@ -13,7 +13,7 @@ from __future__ import annotations
 
 import dataclasses
 import os
-from typing import Callable, List, Optional, Tuple
+from typing import Callable, Optional, Tuple
 
 import torch
 import torch.distributed as dist

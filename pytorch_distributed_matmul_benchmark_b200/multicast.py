@@ -16,7 +16,7 @@ from __future__ import annotations
 import os
 import socket
 import tempfile
-from typing import List, Tuple
+from typing import Tuple
 
 import torch
 import torch.distributed as dist
@@ -34,9 +34,8 @@ def _ok(result, what: str):
     """cuda-python returns (CUresult, value...) tuples; raise on failure, unwrap the value."""
     err = result[0]
     if int(err) != 0:
-        drv = _drv()
-        name = drv.cuGetErrorName(err)[1]
-        raise RuntimeError(f"{what} failed: {name.decode() if isinstance(name, bytes) else name} ({int(err)})")
+        name = getattr(err, "name", None) or str(err)  # the enum's own name; no driver call needed to report an error
+        raise RuntimeError(f"{what} failed: {name} ({int(err)})")
     rest = result[1:]
     return rest[0] if len(rest) == 1 else rest
 

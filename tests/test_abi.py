@@ -88,3 +88,17 @@ def test_cpu_tensors_are_rejected():
     import pytorch_distributed_matmul_benchmark_b200 as b2
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         b2.matmul(torch.zeros(8, 8), torch.zeros(8, 8))
+
+
+def test_multicast_helpers_without_a_gpu():
+    """multicast.py is host plumbing over the cuda-python driver bindings; what can be checked without a device:
+    the raw-memory wrapper torch consumes, and that a driver error becomes a RuntimeError naming the call."""
+    import pytest
+    from pytorch_distributed_matmul_benchmark_b200 import multicast
+    blob = multicast._Blob(0x7f0000000000, 4096)
+    iface = blob.__cuda_array_interface__
+    assert iface["shape"] == (4096,) and iface["typestr"] == "|u1" and iface["data"] == (0x7f0000000000, False)
+    assert multicast._ok((0, 7), "x") == 7 and multicast._ok((0, 1, 2), "x") == (1, 2)
+    drv = multicast._drv()
+    with pytest.raises(RuntimeError, match="cuMemCreate failed"):
+        multicast._ok((drv.CUresult.CUDA_ERROR_OUT_OF_MEMORY, None), "cuMemCreate")

@@ -1,5 +1,4 @@
 """The drop-in scripts end to end on the GPU (single process), and the multi-rank modes when >= 2 GPUs are present."""
-import os
 import re
 import socket
 import subprocess

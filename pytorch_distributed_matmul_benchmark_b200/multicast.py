@@ -115,16 +115,26 @@ class MulticastBuffer:
         prop.size = size
         self.size, self.nbytes = size, nbytes
 
-        # rank 0 creates the multicast object; the others import it from its file descriptor
-        path = [os.path.join(tempfile.gettempdir(), f"b2mm_mc_{os.getpid()}_{id(self):x}.sock")] if rank == 0 else [None]
-        dist.broadcast_object_list(path, src=0)
+        # rank 0 creates the multicast object; the others import it from its file descriptor.  A failure on rank 0
+        # (e.g. multicast disabled by the fabric manager) is broadcast, so that every rank raises instead of waiting
+        payload = [None]
+        fd = -1
         if rank == 0:
-            self._mc = _ok(drv.cuMulticastCreate(prop), "cuMulticastCreate")
-            fd = _ok(drv.cuMemExportToShareableHandle(self._mc, fd_type, 0), "cuMemExportToShareableHandle")
-            _send_fd_to_peers(int(fd), world_size - 1, path[0])
-            os.close(int(fd))
+            try:
+                self._mc = _ok(drv.cuMulticastCreate(prop), "cuMulticastCreate")
+                fd = int(_ok(drv.cuMemExportToShareableHandle(self._mc, fd_type, 0), "cuMemExportToShareableHandle"))
+                payload = [os.path.join(tempfile.gettempdir(), f"b2mm_mc_{os.getpid()}_{id(self):x}.sock")]
+            except RuntimeError as e:
+                payload = [f"ERROR: {e}"]
+        dist.broadcast_object_list(payload, src=0)
+        if payload[0].startswith("ERROR: "):
+            self._closed = True
+            raise RuntimeError(payload[0][len("ERROR: "):])
+        if rank == 0:
+            _send_fd_to_peers(fd, world_size - 1, payload[0])
+            os.close(fd)
         else:
-            fd = _recv_fd(path[0])
+            fd = _recv_fd(payload[0])
             self._mc = _ok(drv.cuMemImportFromShareableHandle(fd, fd_type), "cuMemImportFromShareableHandle")
             os.close(fd)
         _ok(drv.cuMulticastAddDevice(self._mc, dev), "cuMulticastAddDevice")

@@ -350,9 +350,8 @@ class Communicator:
     def gather_buffer(self, M: int, n_local: int, dtype: torch.dtype):
         """The [world][M][n_local] buffer of the fused matrix_parallel path: multicast (one TMA store per chunk, replicated
         by the NVSwitch) where the hardware has it, else peer-mapped (one store per destination).  Collective."""
-        if self.nvls_available():
-            return self.multicast_like(torch.empty((self.world_size, M, n_local), dtype=dtype, device="meta"))
-        return self.shared_slabs(M, n_local, dtype)
+        buf = self._try_multicast(torch.empty((self.world_size, M, n_local), dtype=dtype, device="meta"))
+        return buf if buf is not None else self.shared_slabs(M, n_local, dtype)
 
     def shared_like(self, t: torch.Tensor) -> "SharedSlabs":
         """A buffer shaped like `t` on every rank, each visible to every other rank (for the p2p all_reduce)."""
@@ -382,7 +381,21 @@ class Communicator:
     def reduce_buffer_like(self, t: torch.Tensor):
         """The buffer the fused / co-resident all_reduce paths work on: a multicast (NVLS) buffer where the hardware
         has it, otherwise a peer-mapped one (pull / add / push).  Collective; `.local` is this rank's tensor."""
-        return self.multicast_like(t) if self.nvls_available() else self.shared_like(t)
+        buf = self._try_multicast(t)
+        return buf if buf is not None else self.shared_like(t)
+
+    def _try_multicast(self, t: torch.Tensor):
+        """A multicast buffer, or None when the box cannot make one; the outcome is the same on every rank (rank 0's
+        failure to create the object is broadcast), so all ranks take the peer-mapped path together."""
+        if not self.nvls_available():
+            return None
+        try:
+            return self.multicast_like(t)
+        except RuntimeError as e:
+            if self.rank == 0:
+                print(f"b2mm: NVLS multicast buffer unavailable ({e}); using peer-mapped buffers")
+            self._nvls = False
+            return None
 
     def all_reduce_nvls(self, buf, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """In-place SUM of buf.local over ranks, reduced inside the NVSwitch (multimem.ld_reduce / multimem.st)."""

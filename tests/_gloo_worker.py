@@ -19,6 +19,7 @@ from oracle import oracle, reference_port  # noqa: E402
 from pytorch_distributed_matmul_benchmark_b200 import hostlib  # noqa: E402
 from pytorch_distributed_matmul_benchmark_b200 import matmul_scaling_benchmark as ms  # noqa: E402
 from pytorch_distributed_matmul_benchmark_b200 import matmul_distributed_benchmark as md  # noqa: E402
+from pytorch_distributed_matmul_benchmark_b200 import matmul_overlap_benchmark as ov  # noqa: E402
 
 
 class FakeEvent:
@@ -88,6 +89,8 @@ def main(out_dir: str):
         # the earlier draft's modes (backup/matmul_distributed_benchmark.py); 33 % 2 != 0 exercises the unequal slabs
         for mode in md.BenchmarkMode:
             md.run_benchmarks(rank, ws, [32, 33], torch.float32, mode, 2, 1, ops=ops, device=device, check=True)
+        # the serialised mode of backup/matmul_overlap_benchmark.py (the overlapped ones need CUDA streams)
+        ov.run_benchmarks(rank, ws, [32], torch.float32, ov.BenchmarkMode.NO_OVERLAP, 2, 1, ops=ops, device=device, check=True)
     finally:
         sys.stdout = real_stdout
         log.close()

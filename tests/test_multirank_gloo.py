@@ -62,10 +62,21 @@ def test_report_for_two_ranks(gloo_run):
 def test_distributed_draft_modes_for_two_ranks(gloo_run):
     """independent / data_parallel / model_parallel of backup/matmul_distributed_benchmark.py, world size 2."""
     _, report, other = gloo_run
-    part = report[report.index("Distributed Matrix Multiplication Benchmark"):]
+    part = report[report.index("Distributed Matrix Multiplication Benchmark"):report.index("Overlapped Communication/Computation Benchmark")]
     assert "FAIL" not in part and "ERROR" not in part
     assert part.count("Results for 32x32") == 3 and part.count("Results for 33x33") == 3  # 33: unequal slabs 16 + 17
     assert part.count("Parity of the reduced product vs float64 sum") == 2  # data_parallel, both sizes
     assert part.count("  - Effective TFLOPS:") == 4 and part.count("  - Total TFLOPS (all GPUs):") == 2
     assert part.count("  - Communication time:") == 4 and part.count("  - Scaling efficiency:") == 4
     assert "Distributed Matrix Multiplication Benchmark" not in other
+
+
+def test_no_overlap_mode_for_two_ranks(gloo_run):
+    """no_overlap of backup/matmul_overlap_benchmark.py (GEMM, wait, all_reduce, wait), world size 2, with the reduced
+    product checked against the float64 sum of both ranks' products."""
+    _, report, other = gloo_run
+    part = report[report.index("Overlapped Communication/Computation Benchmark"):]
+    assert "  - Mode: no_overlap" in part and "Results for 32x32" in part and "ERROR" not in part
+    assert "Parity of the reduced product vs float64 sum" in part and "FAIL" not in part
+    assert "  - Note: In data parallel, each GPU does full matrix multiply" in part
+    assert "Overlapped Communication/Computation Benchmark" not in other

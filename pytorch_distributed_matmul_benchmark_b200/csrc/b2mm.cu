@@ -355,9 +355,9 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
   if (m_blocks != 1 && m_blocks != 2) {
     const int64_t tall_tiles = ((M + 511) / 512) * ((N + 255) / 256) * batch;
     m_blocks = (tall_tiles >= clusters) ? 2 : 1;
-    // With remote destinations the epilogue drains at NVLink speed: keep TMEM double buffered so
-    // the next tile's main loop runs meanwhile.
-    if (fanout > 1) m_blocks = 1;
+    // With remote destinations (peer mappings, or one multicast address) the epilogue drains at NVLink
+    // speed: keep TMEM double buffered so the next tile's main loop runs meanwhile.
+    if (fanout > 0) m_blocks = 1;
   }
 
   if (dtype == B2MM_BF16) {

@@ -32,7 +32,7 @@ for block in sass.split("Function : ")[1:]:
     ops = collections.Counter()
     n = 0
     for line in block.splitlines():
-        m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", line)
+        m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Za-z0-9_.]*)", line)
         if not m:
             continue
         n += 1

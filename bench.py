@@ -43,6 +43,8 @@ UNIT = "TFLOP/s"
 FLOP = 2.0 * N ** 3
 SPEC_PEAK = 2250.0  # B200 dense bf16, TFLOP/s
 BAD_REASONS = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")
+# One workload for both arms (the driver divides one by the other): the 16384^3 bf16 product, per GPU.
+WORKLOAD = f"{N}x{N}x{N} bfloat16 GEMM per GPU (BASELINE.json configs[1]; independent mode for N>1)"
 
 
 def measured_peaks() -> dict:
@@ -140,8 +142,8 @@ def run_reference(args) -> None:
     line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": base["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"{N}x{N}x{N} bfloat16 GEMM, reference CPU path (torch.matmul, matmul_benchmark.py:69-74)",
-                       "sizes": [N], "mode": "independent"},
+            "config": {"workload": WORKLOAD, "sizes": [N], "mode": "independent",
+                       "arm": "reference CPU path: torch.matmul on the host cores, timed as matmul_benchmark.py:69-74, rank 0 only"},
             "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "config1")},
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -269,8 +271,7 @@ def run_b2mm(args) -> None:
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": f"{N}x{N}x{N} bfloat16 GEMM per GPU (BASELINE.json configs[1]; independent mode for N>1)",
-                       "sizes": [N], "mode": "independent", "parallelism": f"replicas x{world}, no data-path collective",
+            "config": {"workload": WORKLOAD, "sizes": [N], "mode": "independent", "parallelism": f"replicas x{world}, no data-path collective",
                        "l2": "inputs (2 x 512 MiB) and output (512 MiB) exceed the 126 MB L2; no flush needed",
                        "per_gpu_tflops": value / world, "pct_of_spec_dense_peak": 100.0 * value / world / SPEC_PEAK},
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,

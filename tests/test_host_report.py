@@ -217,3 +217,38 @@ def test_model_parallel_slab_storage():
             s, e = hostlib.split_columns(N, ws, r)
             slabs[r, :, :e - s] = full[:, s:e]
         assert torch.equal(hostlib.assemble_slabs(slabs, N, ws), full)
+
+
+# ---- backup/compare_benchmarks.py: the four-run comparison --------------------------------------------------------
+def test_compare_benchmarks_filters_the_reference_reports(host_logic):
+    """The block filter of backup/compare_benchmarks.py:22-26, applied to report text the reference itself printed."""
+    import compare_benchmarks as cb
+    blk = cb.block_for_size(host_logic["report_md_data_parallel_ws2"], 16384)
+    assert blk[0] == "Results for 16384x16384:" and any("Communication overhead" in l for l in blk)
+    assert cb.headline(blk) == (7.0, 1599.29)  # "Total time per operation: 7.000 ms", "Effective TFLOPS: 1599.29"
+    blk = cb.block_for_size(host_logic["report_mb_bf16"], 16384)
+    assert cb.headline(blk) == (5.5, 1599.29) and not any("4096" in l for l in blk)
+    blk = cb.block_for_size(host_logic["report_ov_overlap"], 4096)
+    assert blk and cb.headline(blk)[0] == 5.5
+    assert cb.block_for_size(host_logic["report_ov_overlap"], 8192) == []
+    assert [r[1:] for r in cb.RUNS] == [("run_benchmark.sh", None), ("run_distributed_benchmark.sh", "data_parallel"),
+                                       ("run_overlap_benchmark.sh", "no_overlap"), ("run_overlap_benchmark.sh", "overlap")]
+
+
+def test_compare_benchmarks_end_to_end_against_a_stub(host_logic, tmp_path):
+    """All four launchers run (python3 replaced by a stub that prints a recorded reference report); the summary table
+    carries the parsed time and TFLOPS of each."""
+    import sys
+    report = tmp_path / "report.txt"
+    report.write_text(host_logic["report_md_data_parallel_ws2"])
+    stub = tmp_path / "python3"
+    stub.write_text(f"#!/bin/bash\ncat {report}\n")
+    stub.chmod(0o755)
+    env = dict(os.environ, PATH=str(tmp_path) + os.pathsep + os.environ["PATH"])
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "compare_benchmarks.py"), "--gpus", "2"], env=env, capture_output=True,
+                       text=True, check=True)
+    assert p.stdout.count("Results for 16384x16384:") == 4 and "### TEST 4: Overlap Benchmark - With Overlap" in p.stdout
+    assert p.stdout.count("    7.000 ms    1599.29 TFLOPS") == 4
+    dry = subprocess.run([sys.executable, os.path.join(ROOT, "compare_benchmarks.py"), "--dry-run", "--check"], capture_output=True,
+                         text=True, check=True).stdout
+    assert "run_distributed_benchmark.sh 2 data_parallel bfloat16 --check" in dry and "run_benchmark.sh 2 bfloat16 --check" in dry

@@ -6,7 +6,7 @@ from conftest import ROOT
 
 PRODUCT_DIRS = ["pytorch_distributed_matmul_benchmark_b200", "include"]
 PRODUCT_FILES = ["matmul_benchmark.py", "matmul_scaling_benchmark.py", "matmul_overlap_benchmark.py",
-                 "matmul_distributed_benchmark.py", "run_benchmark.sh", "run_scaling_benchmark.sh", "run_overlap_benchmark.sh",
+                 "matmul_distributed_benchmark.py", "compare_benchmarks.py", "run_benchmark.sh", "run_scaling_benchmark.sh", "run_overlap_benchmark.sh",
                  "run_distributed_benchmark.sh", "run_common.sh"]
 PAT = re.compile(r"^\s*(from|import)\s+oracle\b|liboracle|oracle/_build|oracle\.gemm|gemm_oracle", re.M)
 

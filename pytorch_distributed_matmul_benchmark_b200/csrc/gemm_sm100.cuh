@@ -40,6 +40,15 @@
 // L2 demand), so a static split finishes at the pace of the slowest SM and its clusters drift
 // apart in k, which destroys their sharing of A/B panels in L2.
 //
+// Output.  Staged through 128B-swizzled shared memory and written with TMA stores, which clip rows exactly
+// but columns only at 16-byte granularity; when N * sizeof(OutT) is not a multiple of 16 the chunk that
+// straddles N is written with element stores instead (store_row_tail), so nothing outside M x N is touched.
+// With GemmParams::fanout the same chunk goes to several destinations (peer mappings, or one multicast
+// address that the NVSwitch replicates): the all_gather of matrix_parallel done by the epilogue.
+//
+// Launch.  Programmatic dependent launch: launch_dependents on entry, griddepcontrol.wait after the
+// prologue and before the first global access, so the next GEMM's CTAs set up while this one drains.
+//
 // kSplit == 2 is the fp32 path (3xTF32): A and B^T each arrive as a (hi, lo)
 // pair of TF32-exact fp32 arrays (written by the split kernels at the end of
 // this file) and every k-step issues

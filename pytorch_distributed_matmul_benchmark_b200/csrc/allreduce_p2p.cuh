@@ -20,6 +20,18 @@ struct PeerPtrs {
   void* p[8];
 };
 
+// Element `i` of a pointer table that arrives as a kernel parameter.  Indexing such a table with a run-time value
+// makes the compiler copy it to local memory (LDL on every use); eight compare-selects on constant indices keep it
+// in the constant bank / registers instead.
+template <class Ptr>
+__device__ __forceinline__ Ptr pick(const Ptr (&p)[8], int i) {
+  Ptr v = p[0];
+#pragma unroll
+  for (int d = 1; d < 8; ++d)
+    if (i == d) v = p[d];
+  return v;
+}
+
 template <typename T>
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]);
 template <>
@@ -63,16 +75,23 @@ __device__ __forceinline__ uint4 pack8<__half>(const float (&f)[8]) {
 
 // `vec_begin`/`vec_count`: this launch's range in 16-byte vectors (already restricted to the slice
 // this rank owns).  kUnroll independent vectors per thread keep enough loads in flight for NVLink.
-template <typename T, int kUnroll>
-__global__ void __launch_bounds__(512) allreduce_p2p_kernel(PeerPtrs ptrs, int world, int64_t vec_begin, int64_t vec_count) {
+// The pull / add / push loop shared by both kernels below.  kWorld is the world size as a compile-time constant
+// (2, 4, 8: every index into `ptrs` is then a constant and the table never leaves the parameter bank), or 0 for
+// any other world <= 8 (the same 8-way unroll, each step predicated on the run-time `world`).
+template <typename T, int kUnroll, int kWorld>
+__device__ __forceinline__ void pull_add_push(const PeerPtrs& ptrs, int world, int64_t vec_begin, int64_t vec_count) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  constexpr int kLanes = sizeof(T) == 4 ? 4 : 8;
+  constexpr int kMax = kWorld > 0 ? kWorld : 8;  // kWorld == 0: any world <= 8, every step predicated on r < world
   for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < vec_count; base += stride * kUnroll) {
-    float acc[kUnroll][sizeof(T) == 4 ? 4 : 8];
+    float acc[kUnroll][kLanes];
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u)
 #pragma unroll
-      for (int j = 0; j < (sizeof(T) == 4 ? 4 : 8); ++j) acc[u][j] = 0.f;
-    for (int r = 0; r < world; ++r) {
+      for (int j = 0; j < kLanes; ++j) acc[u][j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < kMax; ++r) {
+      if (kWorld == 0 && r >= world) break;
       const uint4* src = reinterpret_cast<const uint4*>(ptrs.p[r]) + vec_begin;
       uint4 v[kUnroll];
 #pragma unroll
@@ -107,13 +126,21 @@ __global__ void __launch_bounds__(512) allreduce_p2p_kernel(PeerPtrs ptrs, int w
         } else {
           out = pack8<T>(acc[u]);
         }
-        for (int d = 0; d < world; ++d) {
+#pragma unroll
+        for (int d = 0; d < kMax; ++d) {
+          if (kWorld == 0 && d >= world) break;
           uint4* dst = reinterpret_cast<uint4*>(ptrs.p[d]) + vec_begin + i;
           asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(out.x), "r"(out.y), "r"(out.z), "r"(out.w) : "memory");
         }
       }
     }
   }
+}
+
+template <typename T, int kUnroll, int kWorld>
+__global__ void __launch_bounds__(512) allreduce_p2p_kernel(const __grid_constant__ PeerPtrs ptrs, int world, int64_t vec_begin,
+                                                            int64_t vec_count) {
+  pull_add_push<T, kUnroll, kWorld>(ptrs, world, vec_begin, vec_count);
 }
 
 // ---- the same reduction with its cross-GPU synchronisation inside the kernel -----------------
@@ -163,8 +190,8 @@ __device__ __forceinline__ void sync_reduce_prologue(const SignalPtrs& sig, int 
   }
   if (band_counter != nullptr) __syncthreads();
   if ((int)threadIdx.x < world) {
-    if (blockIdx.x == 0) st_release_sys(sig.p[threadIdx.x] + rank, epoch);  // my panel is complete (kernel order)
-    wait_epoch(sig.p[rank] + threadIdx.x, epoch);                           // ... and so is everybody else's
+    if (blockIdx.x == 0) st_release_sys(pick(sig.p, (int)threadIdx.x) + rank, epoch);  // my panel is complete (kernel order)
+    wait_epoch(pick(sig.p, rank) + threadIdx.x, epoch);                                 // ... and so is everybody else's
   }
   __syncthreads();
 }
@@ -172,64 +199,13 @@ __device__ __forceinline__ void sync_reduce_prologue(const SignalPtrs& sig, int 
 // Needs no shared memory and few registers on purpose: its CTAs are meant to be co-resident with the
 // GEMM's (which own all of an SM's shared memory but few of its threads), so the reduction of panel i
 // runs on the same SMs as the GEMM of panel i+1 and nothing has to be reserved for it.
-template <typename T, int kUnroll>
-__global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(PeerPtrs ptrs, SignalPtrs sig, int rank, int world, int epoch,
-                                                                  int64_t vec_begin, int64_t vec_count,
+template <typename T, int kUnroll, int kWorld>
+__global__ void __launch_bounds__(256) allreduce_p2p_sync_kernel(const __grid_constant__ PeerPtrs ptrs,
+                                                                  const __grid_constant__ SignalPtrs sig, int rank, int world,
+                                                                  int epoch, int64_t vec_begin, int64_t vec_count,
                                                                   const int* band_counter, int band_target) {
   sync_reduce_prologue(sig, rank, world, epoch, band_counter, band_target);
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  constexpr int kLanes = sizeof(T) == 4 ? 4 : 8;
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < vec_count; base += stride * kUnroll) {
-    float acc[kUnroll][kLanes];
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u)
-#pragma unroll
-      for (int j = 0; j < kLanes; ++j) acc[u][j] = 0.f;
-    for (int r = 0; r < world; ++r) {
-      const uint4* src = reinterpret_cast<const uint4*>(ptrs.p[r]) + vec_begin;
-      uint4 v[kUnroll];
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int64_t i = base + u * stride;
-        if (i < vec_count) asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i));
-      }
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        if (base + u * stride < vec_count) {
-          if constexpr (sizeof(T) == 4) {
-            acc[u][0] += __uint_as_float(v[u].x);
-            acc[u][1] += __uint_as_float(v[u].y);
-            acc[u][2] += __uint_as_float(v[u].z);
-            acc[u][3] += __uint_as_float(v[u].w);
-          } else {
-            float f[8];
-            unpack8<T>(v[u], f);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[u][j] += f[j];
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-      const int64_t i = base + u * stride;
-      if (i < vec_count) {
-        uint4 out;
-        if constexpr (sizeof(T) == 4) {
-          out = make_uint4(__float_as_uint(acc[u][0]), __float_as_uint(acc[u][1]), __float_as_uint(acc[u][2]), __float_as_uint(acc[u][3]));
-        } else {
-          float f[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = acc[u][j];
-          out = pack8<T>(f);
-        }
-        for (int d = 0; d < world; ++d) {
-          uint4* dst = reinterpret_cast<uint4*>(ptrs.p[d]) + vec_begin + i;
-          asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(out.x), "r"(out.y), "r"(out.z), "r"(out.w) : "memory");
-        }
-      }
-    }
-  }
+  pull_add_push<T, kUnroll, kWorld>(ptrs, world, vec_begin, vec_count);
 }
 
 // ---- the same, reduced INSIDE the NVSwitch (NVLS) ---------------------------------------------
@@ -266,7 +242,7 @@ __device__ __forceinline__ void multimem_st(uint4* mc, const uint4& v) {
 }
 
 template <typename T, int kUnroll>
-__global__ void __launch_bounds__(256) allreduce_nvls_sync_kernel(void* mc, SignalPtrs sig, int rank, int world, int epoch,
+__global__ void __launch_bounds__(256) allreduce_nvls_sync_kernel(void* mc, const __grid_constant__ SignalPtrs sig, int rank, int world, int epoch,
                                                                    int64_t vec_begin, int64_t vec_count,
                                                                    const int* band_counter, int band_target) {
   sync_reduce_prologue(sig, rank, world, epoch, band_counter, band_target);
@@ -289,11 +265,11 @@ __global__ void __launch_bounds__(256) allreduce_nvls_sync_kernel(void* mc, Sign
 
 // After the last reduction of a call: tell every rank that this rank's pushes have landed, then wait for
 // the same from every rank.  One warp.
-__global__ void p2p_done_kernel(SignalPtrs sig, int rank, int world, int epoch) {
+__global__ void p2p_done_kernel(const __grid_constant__ SignalPtrs sig, int rank, int world, int epoch) {
   if ((int)threadIdx.x < world) {
     __threadfence_system();
-    st_release_sys(sig.p[threadIdx.x] + 8 + rank, epoch);
-    wait_epoch(sig.p[rank] + 8 + threadIdx.x, epoch);
+    st_release_sys(pick(sig.p, (int)threadIdx.x) + 8 + rank, epoch);
+    wait_epoch(pick(sig.p, rank) + 8 + threadIdx.x, epoch);
   }
 }
 

@@ -105,6 +105,18 @@ static GemmOpts overlap_opts() {
   return o;
 }
 
+static constexpr int kSyncUnroll = 4;
+
+template <typename T>
+static void carveout_for_type() {
+  const int co = cudaSharedmemCarveoutMaxShared;
+  cudaFuncSetAttribute(allreduce_p2p_sync_kernel<T, kSyncUnroll, 2>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+  cudaFuncSetAttribute(allreduce_p2p_sync_kernel<T, kSyncUnroll, 4>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+  cudaFuncSetAttribute(allreduce_p2p_sync_kernel<T, kSyncUnroll, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+  cudaFuncSetAttribute(allreduce_p2p_sync_kernel<T, kSyncUnroll, 0>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+  cudaFuncSetAttribute(allreduce_nvls_sync_kernel<T, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+}
+
 }  // namespace b2mm
 
 using namespace b2mm;
@@ -345,11 +357,23 @@ static int launch_allreduce_p2p(void* const* peers, int rank, int world, int64_t
   int ctas = (v && *v) ? atoi(v) : 32;
   if (ctas < 1) ctas = 1;
   constexpr int kUnroll = 4;
-  switch (dtype) {
-    case B2MM_BF16: allreduce_p2p_kernel<__nv_bfloat16, kUnroll><<<ctas, 512, 0, stream>>>(pp, world, begin, mine); break;
-    case B2MM_FP16: allreduce_p2p_kernel<__half, kUnroll><<<ctas, 512, 0, stream>>>(pp, world, begin, mine); break;
-    default: allreduce_p2p_kernel<float, kUnroll><<<ctas, 512, 0, stream>>>(pp, world, begin, mine); break;
+  // world as a template argument (2 / 4 / 8; 0 = any other size, predicated): the peer table is then only ever
+  // indexed by constants and stays in the parameter bank
+#define B2MM_P2P(T, W) allreduce_p2p_kernel<T, kUnroll, W><<<ctas, 512, 0, stream>>>(pp, world, begin, mine)
+#define B2MM_P2P_WORLD(T)                                                                      \
+  switch (world) {                                                                             \
+    case 2: B2MM_P2P(T, 2); break;                                                             \
+    case 4: B2MM_P2P(T, 4); break;                                                             \
+    case 8: B2MM_P2P(T, 8); break;                                                             \
+    default: B2MM_P2P(T, 0); break;                                                            \
   }
+  switch (dtype) {
+    case B2MM_BF16: B2MM_P2P_WORLD(__nv_bfloat16) break;
+    case B2MM_FP16: B2MM_P2P_WORLD(__half) break;
+    default: B2MM_P2P_WORLD(float) break;
+  }
+#undef B2MM_P2P_WORLD
+#undef B2MM_P2P
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "p2p all_reduce launch failed: %s", cudaGetErrorString(e));
   count_launch(1);
@@ -403,21 +427,16 @@ int b2mm_gemm_allreduce_p2p(void* comm, const void* A, const void* B, void* cons
 
 // CTAs of two kernels share an SM only if both ask for the same L1/shared-memory split: the GEMM runs with
 // the maximum shared-memory carve-out, so the (shared-memory-free) reduction kernels ask for it too.
-static constexpr int kSyncUnroll = 4;
 static void prefer_gemm_carveout() {
   static std::once_flag once[64];
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) return;
   std::call_once(once[dev], [] {
-    const int co = cudaSharedmemCarveoutMaxShared;
-    cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__nv_bfloat16, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-    cudaFuncSetAttribute(allreduce_p2p_sync_kernel<__half, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-    cudaFuncSetAttribute(allreduce_p2p_sync_kernel<float, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__nv_bfloat16, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<__half, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-    cudaFuncSetAttribute(allreduce_nvls_sync_kernel<float, kSyncUnroll>, cudaFuncAttributePreferredSharedMemoryCarveout, co);
-    cudaFuncSetAttribute(p2p_done_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, co);
+    carveout_for_type<__nv_bfloat16>();
+    carveout_for_type<__half>();
+    carveout_for_type<float>();
+    cudaFuncSetAttribute(p2p_done_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   });
 }
 
@@ -448,11 +467,22 @@ static int launch_sync_reduce(Comm* c, const PeerPtrs& pp, const SignalPtrs& sp,
     count_launch(1);
     return B2MM_OK;
   }
-  switch (dtype) {
-    case B2MM_BF16: allreduce_p2p_sync_kernel<__nv_bfloat16, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
-    case B2MM_FP16: allreduce_p2p_sync_kernel<__half, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
-    default: allreduce_p2p_sync_kernel<float, kSyncUnroll><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target); break;
+#define B2MM_SYNC(T, W) \
+  allreduce_p2p_sync_kernel<T, kSyncUnroll, W><<<ctas, 256, 0, cs>>>(pp, sp, c->rank, c->world, epoch, begin, mine, band_counter, band_target)
+#define B2MM_SYNC_WORLD(T)                                                                     \
+  switch (c->world) {                                                                          \
+    case 2: B2MM_SYNC(T, 2); break;                                                            \
+    case 4: B2MM_SYNC(T, 4); break;                                                            \
+    case 8: B2MM_SYNC(T, 8); break;                                                            \
+    default: B2MM_SYNC(T, 0); break;                                                           \
   }
+  switch (dtype) {
+    case B2MM_BF16: B2MM_SYNC_WORLD(__nv_bfloat16) break;
+    case B2MM_FP16: B2MM_SYNC_WORLD(__half) break;
+    default: B2MM_SYNC_WORLD(float) break;
+  }
+#undef B2MM_SYNC_WORLD
+#undef B2MM_SYNC
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "peer all_reduce launch failed: %s", cudaGetErrorString(e));
   count_launch(1);

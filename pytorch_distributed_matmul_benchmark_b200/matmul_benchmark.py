@@ -50,11 +50,8 @@ def benchmark_matmul(matrix_size: int, dtype: torch.dtype, device: str, num_iter
     total_time = start_event.elapsed_time(end_event) / 1000.0
     avg_time = total_time / num_iterations
     if check and C is not None:
-        err = hostlib.parity_error(C, A, B)
-        tol = hostlib.CHECK_TOL[dtype]
-        print(f"  Parity vs float64 reference: max err {err:.3e} (tolerance {tol:.1e}) -> {'OK' if err <= tol else 'FAIL'}")
-        if err > tol:
-            raise RuntimeError(f"parity check failed: {err:.3e} > {tol:.1e}")
+        hostlib.report_check(dist.get_rank() if dist.is_initialized() else 0, hostlib.parity_error(C, A, B),
+                             hostlib.CHECK_TOL[dtype], "vs float64 reference", indent="  ", device=device)
     return avg_time, calculate_tflops(matrix_size, avg_time)
 
 

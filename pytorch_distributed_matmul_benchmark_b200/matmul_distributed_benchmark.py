@@ -142,10 +142,7 @@ def benchmark_model_parallel(matrix_size: int, dtype: torch.dtype, device: str, 
 
 
 def _report_check(rank: int, err: float, tol: float) -> None:
-    if rank == 0:
-        print(f"    Parity vs float64 reference: max err {err:.3e} (tolerance {tol:.1e}) -> {'OK' if err <= tol else 'FAIL'}")
-    if err > tol:
-        raise RuntimeError(f"parity check failed on rank {rank}: {err:.3e} > {tol:.1e}")
+    hostlib.report_check(rank, err, tol, "vs float64 reference", device=hostlib.rank_device(rank))
 
 
 def _f32(x: float) -> float:

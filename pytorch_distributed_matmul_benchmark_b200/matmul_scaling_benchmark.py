@@ -109,7 +109,7 @@ def benchmark_independent(matrix_size: int, dtype: torch.dtype, device: str, ran
 
     avg_time = _timed_loop(ops, step, num_iterations)
     if check and C is not None:
-        _report_check(rank, hostlib.parity_error(C, A, B), dtype)
+        _report_check(rank, hostlib.parity_error(C, A, B), dtype, device)
     return avg_time, calculate_tflops(matrix_size, avg_time, num_ops=1)
 
 
@@ -149,7 +149,7 @@ def benchmark_batch_parallel(matrix_size: int, batch_size: int, dtype: torch.dty
     if check and local_batch_size > 0:
         ops.bmm(A, B, out=C)
         ops.synchronize()
-        _report_check(rank, hostlib.parity_error(C, A, B), dtype)
+        _report_check(rank, hostlib.parity_error(C, A, B), dtype, device)
 
     if overlap and comm_on and local_batch_size > 0 and ops.bmm_allreduce_overlap is not None:
         for _ in range(min(warmup_iterations, 3)):
@@ -171,14 +171,18 @@ def benchmark_batch_parallel(matrix_size: int, batch_size: int, dtype: torch.dty
         avg_fused = _timed_loop(ops, lambda: ops.bmm_allreduce_fused(A, B, shared, panels), num_iterations)
         if rank == 0:
             print(f"    Fused GEMM+all_reduce ({how}) end-to-end: {avg_fused*1000:.3f} ms ({panels} panels; serial sum {(avg_compute_time + avg_comm_time)*1000:.3f} ms)")
-        if check:  # against the NCCL all_reduce of the same product: two roundings of one sum, at most ~1 ulp apart
+        if check:
+            # Against the NCCL all_reduce of the same rounded products (what the reference computes, :142-150).  Both are
+            # roundings of one sum: the fused path rounds once, NCCL once (NVLS / 2 ranks) or once per ring step, so
+            # the two may sit one output ulp apart per rounding — 2 x tolerance, whatever the world size.
             ops.bmm(A, B, out=C)
             ops.all_reduce(C)
             ops.synchronize()
             ref = C.double()
             rms = ref.pow(2).mean().sqrt()
             err = ((shared.local.double() - ref).abs() / (ref.abs() + rms)).max().item()
-            _report_check(rank, err / 2 / max(world_size // 2, 1), dtype)
+            hostlib.report_check(rank, err, 2 * hostlib.CHECK_TOL[dtype], "of the fused all_reduce vs NCCL all_reduce of the same products",
+                                 device=device)
         avg_total_time = avg_fused
 
     tflops_per_gpu = calculate_tflops(matrix_size, avg_total_time, num_ops=local_batch_size) if avg_total_time > 0 else 0.0
@@ -267,18 +271,14 @@ def benchmark_matrix_parallel(matrix_size: int, dtype: torch.dtype, device: str,
     if check and B_full is not None:
         ops.synchronize()
         C_global = hostlib.assemble_slabs(slabs, matrix_size, world_size)  # [N][N]: slab r holds columns of rank r
-        _report_check(rank, hostlib.parity_error(C_global, A, B_full), dtype)
+        _report_check(rank, hostlib.parity_error(C_global, A, B_full), dtype, device)
 
     tflops_per_gpu = calculate_tflops(matrix_size, avg_total_time, num_ops=1) / world_size
     return avg_total_time, tflops_per_gpu
 
 
-def _report_check(rank: int, err: float, dtype: torch.dtype) -> None:
-    tol = hostlib.CHECK_TOL[dtype]
-    if rank == 0:
-        print(f"    Parity vs float64 reference: max err {err:.3e} (tolerance {tol:.1e}) -> {'OK' if err <= tol else 'FAIL'}")
-    if err > tol:
-        raise RuntimeError(f"parity check failed on rank {rank}: {err:.3e} > {tol:.1e}")
+def _report_check(rank: int, err: float, dtype: torch.dtype, device: Optional[str] = None) -> None:
+    hostlib.report_check(rank, err, hostlib.CHECK_TOL[dtype], "vs float64 reference", device=device)
 
 
 def run_benchmarks(rank: int, world_size: int, matrix_sizes: List[int], dtype: torch.dtype, mode: ScalingMode,

@@ -440,13 +440,16 @@ class Communicator:
         return t
 
     def bmm_allreduce_fused(self, A: torch.Tensor, B: torch.Tensor, shared_C: "SharedSlabs", n_panels: int = 4) -> torch.Tensor:
-        """C = bmm(A, B) in row panels; each panel summed over ranks by a self-synchronising peer-memory kernel
-        that shares the SMs with the next panel's GEMM (no NCCL, nothing reserved)."""
+        """C = bmm(A, B) as one GEMM whose epilogue publishes finished row bands; each band is summed over ranks by a
+        self-synchronising kernel (in the NVSwitch, or over peer mappings) that shares the SMs with the rest of the
+        GEMM (no NCCL, nothing reserved).  `n_panels` = row bands per batch element."""
         _require_cuda(A, B)
         self._signal_pads()
         b, N, _ = A.shape
         code = _dtype_code(A)
-        ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)
+        # the library runs ONE batched GEMM over the whole local batch (the bands are only its signalling unit), so the
+        # fp32 split scratch is sized for the whole batch, not for one row panel
+        ws, ws_bytes = workspace_for(N, N, N, b, code, A.device)
         self.comm_stream.wait_stream(torch.cuda.current_stream())
         if hasattr(shared_C, "mc_ptr"):  # MulticastBuffer: the bands are reduced inside the NVSwitch
             _lib.check(_lib.load().b2mm_gemm_allreduce_nvls(

@@ -16,7 +16,7 @@ from oracle import oracle, reference_port  # noqa: E402
 import pytorch_distributed_matmul_benchmark_b200 as b2  # noqa: E402
 from pytorch_distributed_matmul_benchmark_b200 import _lib, hostlib  # noqa: E402
 
-TOL = {torch.bfloat16: 4e-3, torch.float16: 5e-4, torch.float32: 2e-5}
+TOL = {torch.bfloat16: 4e-3, torch.float16: 5e-4, torch.float32: 1e-5}
 
 
 def rel(C, ref):
@@ -81,21 +81,38 @@ def main(out_path):
     torch.cuda.synchronize()
     res["fused_allgather_equals_nccl_path"] = torch.equal(slabs, shared.local)
 
-    # batch_parallel, fused GEMM + all_reduce: sum over ranks of the per-rank products
-    Ab, Bb = reference_port.batch_parallel_inputs(rank, ws, 1024, torch.bfloat16, batch_size=2 * ws, device=dev)
+    # batch_parallel, fused GEMM + all_reduce: sum over ranks of the per-rank products.  The expectation comes from
+    # the ORACLE (each rank's product rounded once to the storage type, as the reference reduces rounded C tensors,
+    # matmul_scaling_benchmark.py:142-150), summed in float64 — never from the kernel under test.
+    def oracle_sum(dt, n, local_b):
+        want = 0
+        for r in range(ws):
+            Ar, Br = reference_port.batch_parallel_inputs(r, ws, n, dt, batch_size=local_b * ws, device="cpu")
+            want = want + oracle.gemm(Ar, Br).double()
+        return want
+
+    Ab, Bb = reference_port.batch_parallel_inputs(rank, ws, 1024, torch.bfloat16, batch_size=2 * ws, device="cpu")
+    Ab, Bb = Ab.to(dev), Bb.to(dev)  # drawn on the CPU so that the oracle sees the very same inputs
+    want = oracle_sum(torch.bfloat16, 1024, 2)
     shC = comm.shared_like(torch.empty(2, 1024, 1024, dtype=torch.bfloat16, device=dev))
     for _ in range(2):
         comm.bmm_allreduce_fused(Ab, Bb, shC, 2)
     torch.cuda.synchronize()
-    want = 0
-    for r in range(ws):
-        Ar, Br = reference_port.batch_parallel_inputs(r, ws, 1024, torch.bfloat16, batch_size=2 * ws, device=dev)
-        want = want + b2.bmm(Ar, Br).double()  # each rank's bf16 C, as the reference reduces rounded C tensors
-    res["fused_allreduce"] = rel(shC.local, want) <= TOL[torch.bfloat16]
+    res["fused_allreduce"] = rel(shC.local, want) <= TOL[torch.bfloat16]  # fp32 adds, ONE rounding to nearest
     Cn = b2.bmm(Ab, Bb)
     comm.all_reduce(Cn)
     torch.cuda.synchronize()
-    res["fused_allreduce_vs_nccl"] = rel(shC.local, Cn.double()) <= (ws - 1) * TOL[torch.bfloat16]
+    res["nccl_allreduce_of_products"] = rel(Cn, want) <= max(ws - 1, 1) * TOL[torch.bfloat16]  # a rounding per ring step
+    res["fused_allreduce_vs_nccl"] = rel(shC.local, Cn.double()) <= 2 * TOL[torch.bfloat16]
+    # float32: the fused path runs ONE batched GEMM, its split scratch must cover the whole local batch
+    Af, Bf = reference_port.batch_parallel_inputs(rank, ws, 512, torch.float32, batch_size=2 * ws, device="cpu")
+    Af, Bf = Af.to(dev), Bf.to(dev)
+    want32 = oracle_sum(torch.float32, 512, 2)
+    shF = comm.shared_like(torch.empty(2, 512, 512, dtype=torch.float32, device=dev))
+    for _ in range(2):
+        comm.bmm_allreduce_fused(Af, Bf, shF, 1)
+    torch.cuda.synchronize()
+    res["fused_allreduce_float32"] = rel(shF.local, want32) <= 2 * TOL[torch.float32]  # ws rounded products + one fp32 sum
     # the same reductions done inside the NVSwitch (multicast buffers), where the box has NVLS
     res["nvls_available"] = "yes" if comm.nvls_available() else "no"
     if comm.nvls_available():
@@ -129,8 +146,13 @@ def main(out_path):
         for _ in range(2):
             comm.bmm_allreduce_fused(Ab, Bb, mcC, 2)
         torch.cuda.synchronize()
-        res["fused_allreduce_nvls"] = rel(mcC.local, want) <= 2 * TOL[torch.bfloat16]  # sum of the rounded products, 1 ulp
+        res["fused_allreduce_nvls"] = rel(mcC.local, want) <= 2 * TOL[torch.bfloat16]  # one rounding, by truncation: 1 ulp
         res["fused_allreduce_nvls_vs_peer_path"] = rel(mcC.local, shC.local.double()) <= 2 * TOL[torch.bfloat16]
+        mcF = comm.multicast_like(torch.empty(2, 512, 512, dtype=torch.float32, device=dev))
+        for _ in range(2):
+            comm.bmm_allreduce_fused(Af, Bf, mcF, 1)
+        torch.cuda.synchronize()
+        res["fused_allreduce_nvls_float32"] = rel(mcF.local, want32) <= 2 * TOL[torch.float32]
         comm.release_shared()
 
     # share -> use -> release -> free, more often than the import table is long: mappings are given back (an owner

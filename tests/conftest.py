@@ -22,9 +22,9 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 DTYPES = {"float32": torch.float32, "float16": torch.float16, "bfloat16": torch.bfloat16}
 # max |C - C64| / (|C64| + rms(C64)); SURVEY.md 8(c).  One output ulp for the 16-bit types
-# (2^-8, 2^-11 relative to |C64| + rms, plus fp32 accumulation noise), and fp32-accumulation
-# grade for float32 (torch's own CPU/cuBLAS fp32 results sit at 2e-6 .. 1.4e-5 for K <= 16384).
-TOL = {torch.bfloat16: 4e-3, torch.float16: 5e-4, torch.float32: 2e-5}
+# (2^-8, 2^-11 relative to |C64| + rms, plus fp32 accumulation noise), and 1e-5 for float32 at any K <= 16384
+# (the survey's bar; the 3xTF32 kernel measures 4e-6 .. 5e-6 there, cuBLAS SGEMM 1.4e-5, torch CPU 2e-6).
+TOL = {torch.bfloat16: 4e-3, torch.float16: 5e-4, torch.float32: 1e-5}
 
 
 def pytest_configure(config):

@@ -48,11 +48,14 @@ def test_scaling_script_single_gpu_all_modes(dtype):
                                         ("batch_parallel", ["--overlap", "--panels", "2"]),
                                         ("matrix_parallel", ["--overlap", "--panels", "4"]),
                                         ("matrix_parallel", ["--fused"]),
-                                        ("batch_parallel", ["--fused", "--panels", "2"])])
+                                        ("batch_parallel", ["--fused", "--panels", "2"]),
+                                        ("batch_parallel", ["--fused", "--panels", "2", "--dtype", "float32"]),
+                                        ("matrix_parallel", ["--fused", "--dtype", "float32"])])
 def test_scaling_script_two_gpus(mode, extra):
+    dtype = [] if "--dtype" in extra else ["--dtype", "bfloat16"]
     out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                 "--master-addr=127.0.0.1", f"--master-port={_free_port()}", "matmul_scaling_benchmark.py", "--sizes",
-                "2048", "--iterations", "3", "--warmup", "2", "--dtype", "bfloat16", "--mode", mode, "--check"] + extra)
+                "2048", "--iterations", "3", "--warmup", "2", "--mode", mode, "--check"] + dtype + extra)
     assert "Collective operations verified successfully across 2 GPUs" in out
     assert "Results for 2048x2048:" in out and "ERROR" not in out and "FAIL" not in out
     assert "-> OK" in out

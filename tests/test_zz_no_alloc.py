@@ -64,6 +64,37 @@ def test_two_calls_in_a_row_match_the_workspace_entry_point():
         assert rel_err(got, A.double().cpu() @ B.double().cpu()) <= TOL[torch.float32]
 
 
+def test_the_call_itself_takes_no_device_memory():
+    """The property in the name: with inputs and output already in hand, a call leaves the device's free memory where it was.
+
+    Free memory is read from the driver (cudaMemGetInfo), so an allocation made behind torch's back would show.  The
+    first call on a device is the set-up call (it resolves the array's address, and with lazy module loading that is
+    also when the driver makes room for the library's code and its 32 MiB array), so it is made before the measurement;
+    the calls measured are the ones a caller repeats."""
+    torch.cuda.set_device(0)
+    lib = _lib.load()
+    torch.manual_seed(3)
+    M, N, K = 256, 264, 520
+    A = torch.randn(M, K, dtype=torch.float32, device=DEV)
+    B = torch.randn(K, N, dtype=torch.float32, device=DEV)
+    C = torch.empty(M, N, dtype=torch.float32, device=DEV)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def call():
+        _lib.check(lib.b2mm_gemm_fp32_noalloc(A.data_ptr(), B.data_ptr(), C.data_ptr(), M, N, K, K, N, N, stream))
+        torch.cuda.synchronize()
+
+    call()  # set-up call
+    free_before, _ = torch.cuda.mem_get_info()
+    reserved_before = torch.cuda.memory_reserved()
+    for _ in range(3):
+        call()
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after == free_before, f"free device memory moved by {free_before - free_after} bytes across three calls"
+    assert torch.cuda.memory_reserved() == reserved_before  # nor did it go through torch's allocator
+    assert rel_err(C, A.double().cpu() @ B.double().cpu()) <= TOL[torch.float32]
+
+
 def test_sizes_beyond_the_built_in_scratch_are_refused():
     lib = _lib.load()
     M = N = K = 2048  # needs 64 MiB of split scratch, the array holds 32 MiB

@@ -64,6 +64,11 @@ B2MM_API const char* b2mm_last_error(void);
  * (all threads).  bench.py reports the delta over its timed region. */
 B2MM_API uint64_t b2mm_launch_count(void);
 
+/* Which GEMM kernel configuration the last successful b2mm_gemm-family call ON THIS THREAD launched, as text
+ * (tile shape, CTA pairing, scheduler, grid), e.g. for a benchmark record that must name the kernel it timed
+ * rather than assume it ("" before the first launch).  No counterpart in the reference. */
+B2MM_API const char* b2mm_last_kernel(void);
+
 /* Tools only (scripts/trace_tiles.py): when non-null, every GEMM launched afterwards writes into this
  * device buffer, laid out as rows of 256 uint64 indexed by SM id: row 0 = 1 + the first tile index of the
  * CTA on that SM, row 1 + i = the global-timer value at which its producer started its i-th tile

@@ -19,6 +19,7 @@
 namespace b2mm {
 
 thread_local char g_err[512] = "";
+thread_local char g_last_kernel[256] = "";
 std::atomic<uint64_t> g_launches{0};
 
 int fail(int code, const char* fmt, ...) {
@@ -252,6 +253,12 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, tmA_lo, tmB_lo, *fan, p);
   if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
   count_launch(1);
+  snprintf(g_last_kernel, sizeof(g_last_kernel),
+           "gemm_kernel<cta_group::%d, %dx%d tile per %s, %s, %d-stage TMA ring, %s TMEM%s> %s scheduler, grid %d CTAs",
+           Cfg::kCtaGroup, Cfg::TILE_M, Cfg::BLOCK_N, Cfg::kCtaGroup == 2 ? "CTA pair" : "CTA",
+           o.dtype == B2MM_BF16 ? "bf16" : o.dtype == B2MM_FP16 ? "fp16" : "fp32 as 3xTF32", Cfg::kStages,
+           Cfg::kMBlocks == 2 ? "X/Y halves in" : "double-buffered", Cfg::kChunkKB > 0 ? ", fp32 register carry" : "",
+           p.dynamic ? "dynamic (cluster launch control)" : "static", clusters * Cfg::kCtaGroup);
   return B2MM_OK;
 }
 
@@ -408,6 +415,8 @@ int b2mm_version(void) { return B2MM_VERSION; }
 const char* b2mm_last_error(void) { return b2mm::g_err; }
 
 uint64_t b2mm_launch_count(void) { return b2mm::g_launches.load(std::memory_order_relaxed); }
+
+const char* b2mm_last_kernel(void) { return b2mm::g_last_kernel; }
 
 size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch, int dtype) {
   return b2mm::gemm_workspace_bytes(M, N, K, batch, dtype);

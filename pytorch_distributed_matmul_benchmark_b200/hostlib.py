@@ -108,6 +108,7 @@ class Ops:
     synchronize: Callable = torch.cuda.synchronize
     event: Callable = lambda: torch.cuda.Event(enable_timing=True)
     destroy: Callable = lambda: None
+    comm: object = None  # the ops.Communicator behind the collective fields (None on a single GPU / in CPU tests)
 
 
 def device_ops(rank: int, world_size: int, device: str) -> Ops:
@@ -135,6 +136,7 @@ def device_ops(rank: int, world_size: int, device: str) -> Ops:
         all_reduce_sync=comm.all_reduce_sync if comm else None,
         release_shared=comm.release_shared if comm else (lambda: None),
         destroy=comm.destroy if comm else (lambda: None),
+        comm=comm,
     )
 
 

@@ -44,6 +44,36 @@ def test_peaks_come_from_the_driver_file_or_the_stated_fallback(tmp_path, monkey
     assert bench.measured_peaks() == {"hbm_gbs": 6500.0, "bf16_tflops": 1650.0, "source": "measured"}
 
 
-def test_both_arms_name_one_workload():
+def test_both_arms_share_one_config_dict():
+    """The driver compares the two arms' `config`: both take it from one function, extras live under `notes`."""
     src = open(os.path.join(ROOT, "bench.py")).read()
-    assert src.count('"workload": WORKLOAD') == 2 and "16384" in bench.WORKLOAD and bench.METRIC == "bf16_16k_gemm_tflops"
+    assert src.count('"config": shared_config()') == 2 and src.count('"workload": WORKLOAD') == 1
+    cfg = bench.shared_config()
+    assert cfg == {"workload": bench.WORKLOAD, "sizes": [16384], "mode": "independent"}
+    assert "16384" in bench.WORKLOAD and bench.METRIC == "bf16_16k_gemm_tflops"
+
+
+def test_reference_arm_uses_every_core_it_may_and_reports_the_timed_step():
+    """torch.distributed.run exports OMP_NUM_THREADS=1: the arm must undo that, and ms_per_step is what was timed."""
+    import torch
+    before = torch.get_num_threads()
+    try:
+        torch.set_num_threads(1)
+        bench.N, keep = 512, bench.N  # a small stand-in problem: the logic is size independent
+        try:
+            r = bench.cpu_reference_arm(steps=2, warmup=1, budget_s=1.0)
+        finally:
+            bench.N = keep
+        assert r["cores"] == bench.host_threads() == torch.get_num_threads()
+        assert r["kind"] == "port" and 0 < r["sample_fraction_of_step"] <= 1.0
+        assert abs(r["full_step_ms_extrapolated"] * r["sample_fraction_of_step"] - r["ms_per_step"]) < 1e-9
+    finally:
+        torch.set_num_threads(before)
+
+
+def test_nvml_sampler_window_summarises_samples():
+    s = bench.NvmlSampler.__new__(bench.NvmlSampler)
+    s.samples = [(1.00, 1965, 300.0), (1.01, 1500, 900.0), (1.02, 1400, 1000.0), (2.0, 1965, 250.0)]
+    w = s.window(1.005, 1.5)
+    assert w == {"samples": 2, "sm_mhz_median": 1450.0, "sm_mhz_min": 1400, "power_w_max": 1000.0, "power_w_mean": 950.0}
+    assert s.window(5, 6) == {"samples": 0}

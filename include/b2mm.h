@@ -69,6 +69,12 @@ B2MM_API uint64_t b2mm_launch_count(void);
  * rather than assume it ("" before the first launch).  No counterpart in the reference. */
 B2MM_API const char* b2mm_last_kernel(void);
 
+/* Tools only (scripts/cluster_occupancy.py): how many clusters of `cluster_size` CTAs of the main bf16 GEMM kernel
+ * (one CTA per SM, 227 KB of shared memory) the current device can hold at once, as cudaOccupancyMaxActiveClusters
+ * reports it; -1 on error.  Answers "would 4-CTA clusters (TMA multicast across two CTA pairs) still fill all
+ * 148 SMs?" without launching anything.  No counterpart in the reference. */
+B2MM_API int b2mm_debug_max_active_clusters(int cluster_size);
+
 /* Tools only (scripts/trace_tiles.py): when non-null, every GEMM launched afterwards writes into this
  * device buffer, laid out as rows of 256 uint64 indexed by SM id: row 0 = 1 + the first tile index of the
  * CTA on that SM, row 1 + i = the global-timer value at which its producer started its i-th tile

@@ -115,6 +115,37 @@ def rel_err(C: torch.Tensor, C64: torch.Tensor) -> float:
     return ((C.detach().cpu().double() - C64).abs() / (C64.abs() + rms)).max().item()
 
 
+def reduced_sum_err(got: torch.Tensor, terms64, final_roundings: float = 1.0, ring: bool = False) -> float:
+    """Error of an all_reduce(SUM) of per-rank GEMM outputs, in units of the 8(c) tolerance of the dtype.
+
+    What the reference computes (matmul_scaling_benchmark.py:142-150) is: each rank's product ROUNDED to the storage
+    type, then a sum that is rounded again.  A correct implementation may therefore differ from the exact sum
+    S = sum_r T_r of the unrounded products `terms64` by one 8(c)-grade error per TERM — measured against that term's
+    own magnitude, |T_r| + rms(T_r), not against a sum that may have cancelled — plus `final_roundings` such errors
+    on the sum itself (1: fp32 adds and one rounding to nearest; 2: one rounding by truncation, as the NVSwitch does;
+    with `ring`, world - 1 roundings of partial sums, bounded by the terms' magnitudes).  Returns
+        max |got - S| / (sum_r (|T_r| + rms(T_r)) + final_roundings * (|S| + rms(S)))
+    which a correct result keeps <= the dtype's tolerance (4e-3 bf16, 5e-4 fp16, 1e-5 fp32)."""
+    terms = [t.double() for t in terms64]
+    S = sum(terms)
+    per_term = sum(t.abs() + t.pow(2).mean().sqrt() for t in terms)
+    last = per_term if ring else S.abs() + S.pow(2).mean().sqrt()
+    return ((got.detach().cpu().double() - S).abs() / (per_term + final_roundings * last)).max().item()
+
+
+def gemm_f64(A: torch.Tensor, B: torch.Tensor, threads: int | None = None) -> torch.Tensor:
+    """Unrounded double-precision A @ B (2-D or batched 3-D), row blocks in parallel: the exact-sum side of reduced_sum_err."""
+    A, B = _cpu_rowmajor(A), _cpu_rowmajor(B)
+    if A.dim() == 3:
+        return torch.stack([gemm_f64(A[i], B[i], threads) for i in range(A.shape[0])])
+    M, N = A.shape[0], B.shape[1]
+    threads = threads or min(os.cpu_count() or 1, 32)
+    step = max(1, (M + threads - 1) // threads)
+    with ThreadPoolExecutor(max_workers=threads) as pool:
+        parts = list(pool.map(lambda r0: gemm_block_f64(A, B, r0, min(step, M - r0), 0, N), range(0, M, step)))
+    return torch.cat(parts, dim=0)
+
+
 def calculate_tflops(matrix_size: int, time_seconds: float, num_ops: int = 1) -> float:
     """matmul_benchmark.py:34-37 / matmul_scaling_benchmark.py:63-67."""
     return float(load().oracle_calculate_tflops(matrix_size, time_seconds, num_ops))

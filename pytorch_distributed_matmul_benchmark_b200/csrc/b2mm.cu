@@ -422,6 +422,32 @@ size_t b2mm_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int64_t batch,
   return b2mm::gemm_workspace_bytes(M, N, K, batch, dtype);
 }
 
+int b2mm_debug_max_active_clusters(int cluster_size) {
+  using Cfg = b2mm::GemmConfig<2, 256, 2, 1, __nv_bfloat16, false, 2>;
+  if (cluster_size < 1 || cluster_size > 16) return -1;
+  auto kern = b2mm::gemm_kernel<Cfg>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES) != cudaSuccess) return -1;
+  if (cluster_size > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) return -1;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(148 * 16 / cluster_size * cluster_size, 1, 1);
+  cfg.blockDim = dim3(Cfg::kThreads, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cluster_size;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = -1;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  return n;
+}
+
 void b2mm_debug_set_trace(void* device_buffer) { b2mm::g_trace = (unsigned long long*)device_buffer; }
 
 int b2mm_gemm(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,

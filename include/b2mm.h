@@ -75,6 +75,11 @@ B2MM_API const char* b2mm_last_kernel(void);
  * 148 SMs?" without launching anything.  No counterpart in the reference. */
 B2MM_API int b2mm_debug_max_active_clusters(int cluster_size);
 
+/* Tools only (scripts/fewer_sms_probe.py): park `n_pairs` idle CTA pairs (one whole SM each, sleeping) on the device for
+ * `seconds`, so that what follows in other streams runs on 148 - 2 * n_pairs SMs.  Asynchronous.  Used to measure
+ * how a power-capped GEMM trades SM count for clock.  No counterpart in the reference. */
+B2MM_API int b2mm_debug_occupy_sms(int n_pairs, double seconds, b2mm_stream_t stream);
+
 /* Tools only (scripts/trace_tiles.py): when non-null, every GEMM launched afterwards writes into this
  * device buffer, laid out as rows of 256 uint64 indexed by SM id: row 0 = 1 + the first tile index of the
  * CTA on that SM, row 1 + i = the global-timer value at which its producer started its i-th tile

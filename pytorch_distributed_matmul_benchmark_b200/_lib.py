@@ -33,6 +33,7 @@ SIGNATURES = {
     "b2mm_last_kernel": (c_char_p, []),
     "b2mm_debug_set_trace": (None, [c_void_p]),
     "b2mm_debug_max_active_clusters": (c_int, [c_int]),
+    "b2mm_debug_occupy_sms": (c_int, [c_int, ctypes.c_double, c_void_p]),
     "b2mm_gemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int64, c_int]),
     "b2mm_gemm": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
                           c_int64, c_int64, c_int64, c_int64, c_int, c_void_p, c_size_t, c_void_p]),

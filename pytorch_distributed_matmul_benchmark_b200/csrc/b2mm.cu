@@ -171,6 +171,9 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   } else {
     tmA_lo = tmA;
     tmB_lo = tmB;
+    // tall tiles: the spare A map carries a 128-row box, used by the half tiles of the last wave (see num_work)
+    if (Cfg::kMBlocks == 2)
+      if ((rc = make_map(&tmA_lo, o.A, o.dtype, o.K, o.M, o.batch, o.lda, o.sA, Cfg::BLOCK_K, Cfg::CTA_M / 2))) return rc;
   }
 
   GemmParams p;
@@ -220,7 +223,16 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   if (sms <= 0) return fail(B2MM_ERR_CUDA, "cannot query SM count");
   if (max_sms > 0 && max_sms < sms) sms = max_sms;
   int clusters = sms / Cfg::kCtaGroup;
-  if (clusters > p.num_tiles || p.dynamic) clusters = p.num_tiles;
+  // Last wave at half-tile granularity (tall tiles, dynamic scheduler): with one tile per request the clusters finish
+  // spread over a whole tile period, so on average half a tile period of every SM is idle at the end (1.7 % of a
+  // 16384^3 GEMM); handing out the last `clusters` tiles as 2 x `clusters` half tiles halves that.  Only when the
+  // problem is several waves long, and not with progress counters (their targets count whole tiles).
+  p.split_from = p.num_tiles;
+  if (Cfg::kMBlocks == 2 && Cfg::kSplit == 1 && p.dynamic && !o.band_counter && o.tiles_per_cluster == 0 &&
+      p.num_tiles >= 4 * clusters && env_int("B2MM_SPLIT_TAIL", 1))
+    p.split_from = p.num_tiles - clusters;
+  p.num_work = p.split_from + 2 * (p.num_tiles - p.split_from);
+  if (clusters > p.num_work || p.dynamic) clusters = p.num_work;
   if (clusters < 1) clusters = 1;
 
   auto kern = gemm_kernel<Cfg>;
@@ -258,7 +270,9 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
            Cfg::kCtaGroup, Cfg::TILE_M, Cfg::BLOCK_N, Cfg::kCtaGroup == 2 ? "CTA pair" : "CTA",
            o.dtype == B2MM_BF16 ? "bf16" : o.dtype == B2MM_FP16 ? "fp16" : "fp32 as 3xTF32", Cfg::kStages,
            Cfg::kMBlocks == 2 ? "X/Y halves in" : "double-buffered", Cfg::kChunkKB > 0 ? ", fp32 register carry" : "",
-           p.dynamic ? "dynamic (cluster launch control)" : "static", clusters * Cfg::kCtaGroup);
+           p.dynamic ? (p.num_work > p.num_tiles ? "dynamic (cluster launch control, last wave in half tiles)" : "dynamic (cluster launch control)")
+                     : "static",
+           clusters * Cfg::kCtaGroup);
   return B2MM_OK;
 }
 
@@ -406,6 +420,18 @@ static int noalloc_scratch_address(void** out) {
   return B2MM_OK;
 }
 
+// Tools only: a CTA that owns a whole SM (all of its shared memory) and sleeps until `ns` have passed.
+__global__ void __launch_bounds__(32, 1) occupy_kernel(unsigned long long ns) {
+  extern __shared__ uint8_t occupy_smem[];
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  if (threadIdx.x == 0) occupy_smem[0] = 1;  // the allocation is what keeps other CTAs off this SM
+  do {
+    __nanosleep(20000);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  } while (t - t0 < ns);
+}
+
 }  // namespace b2mm
 
 extern "C" {
@@ -446,6 +472,30 @@ int b2mm_debug_max_active_clusters(int cluster_size) {
     return -1;
   }
   return n;
+}
+
+int b2mm_debug_occupy_sms(int n_pairs, double seconds, b2mm_stream_t stream) {
+  using namespace b2mm;
+  if (n_pairs < 1 || n_pairs > 74 || seconds <= 0 || seconds > 30) return fail(B2MM_ERR_BAD_ARG, "occupy: 1..74 pairs, at most 30 s");
+  constexpr int kSmem = 200 * 1024;
+  cudaError_t e = cudaFuncSetAttribute(occupy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+  if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "occupy: %s", cudaGetErrorString(e));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * n_pairs, 1, 1);
+  cfg.blockDim = dim3(32, 1, 1);
+  cfg.dynamicSmemBytes = kSmem;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;  // pairs: whole TPCs are taken, as a GEMM cluster would take them
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  e = cudaLaunchKernelEx(&cfg, occupy_kernel, (unsigned long long)(seconds * 1e9));
+  if (e != cudaSuccess) return fail(B2MM_ERR_CUDA, "occupy launch: %s", cudaGetErrorString(e));
+  return B2MM_OK;
 }
 
 void b2mm_debug_set_trace(void* device_buffer) { b2mm::g_trace = (unsigned long long*)device_buffer; }

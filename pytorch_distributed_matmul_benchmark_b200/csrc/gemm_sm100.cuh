@@ -67,6 +67,11 @@ struct GemmParams {
   int M, N, K, batch;
   int m_tiles, n_tiles;  // tiles per batch element (cluster tiles)
   int num_tiles;         // m_tiles * n_tiles * batch
+  // Work items handed out by the scheduler.  Items [0, split_from) are whole tiles; every later pair of items is the
+  // upper and lower half (CTA_M / 2 rows per CTA, the X accumulator only) of one of the last tiles, so that the
+  // final wave is balanced at half-tile granularity (kMBlocks == 2 only; split_from == num_tiles: no halves).
+  int num_work;          // split_from + 2 * (num_tiles - split_from)
+  int split_from;
   int num_kb;            // ceil(K / BLOCK_K)
   int group_m;           // tile-rasterisation group height (in tiles)
   uint32_t idesc;        // tcgen05 instruction descriptor
@@ -233,6 +238,17 @@ __device__ __forceinline__ void decode_tile(const GemmParams& p, int tile, int& 
   m_blk = first_m + (in_g - n_blk * gm);
 }
 
+// Work item -> tile index and which part of it: -1 = the whole tile, 0 / 1 = its upper / lower half.
+__device__ __forceinline__ int decode_work(const GemmParams& p, int work, int& half) {
+  if (work < p.split_from) {
+    half = -1;
+    return work;
+  }
+  const int w = work - p.split_from;
+  half = w & 1;
+  return p.split_from + (w >> 1);
+}
+
 template <typename OutT>
 __device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits);
 template <>
@@ -336,7 +352,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   auto next_tile = [&](TileSeq& q, bool warp_collective) -> bool {
     if (!p.dynamic) {
       q.tile += num_clusters;
-      return q.tile < p.num_tiles;
+      return q.tile < p.num_work;
     }
     if (p.max_tiles > 0 && ++q.done >= p.max_tiles) return false;  // every walker counts the same sequence
     mbar_wait(clc_full + 8u * q.slot, q.phase);
@@ -360,11 +376,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t phase = 0;
       TileSeq q{cluster_id, 0, 0u};
       int iter = 0;
-      for (bool more = q.tile < p.num_tiles; more; more = next_tile(q, false), ++iter) {
-        const int tile = q.tile;
+      for (bool more = q.tile < p.num_work; more; more = next_tile(q, false), ++iter) {
+        int half;
+        const int tile = decode_work(p, q.tile, half);
         int b, m_blk, n_blk;
         decode_tile(p, tile, b, m_blk, n_blk);
-        const int m_row = m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M;
+        // a half tile: this CTA's 128 rows of the chosen half, through the 128-row box of tmA_lo
+        const bool is_half = Cfg::kMBlocks == 2 && half >= 0;
+        const int m_row = is_half ? m_blk * Cfg::TILE_M + half * (Cfg::TILE_M / 2) + (int)cta_rank * (Cfg::CTA_M / 2)
+                                  : m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M;
+        const uint32_t stage_tx = (uint32_t)(G * (is_half ? Cfg::STAGE_BYTES - Cfg::kSplit * Cfg::A_BYTES / 2 : Cfg::STAGE_BYTES));
+        const CUtensorMap* mapA = is_half ? &tmA_lo : &tmA;
         const int n_col = n_blk * Cfg::BLOCK_N + (int)cta_rank * Cfg::LOAD_N;
         if (p.trace) {  // row 0: SM id of each CTA; row 1 + i: start time of its i-th tile
           unsigned long long now;
@@ -379,11 +401,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           mbar_wait(empty_bar + 8u * stage, phase ^ 1u);
           const uint32_t fb_local = full_bar + 8u * stage;
           const uint32_t fb = (G == 2) ? mapa(fb_local, 0) : fb_local;
-          if (cta_rank == 0) mbar_arrive_expect_tx(fb_local, (uint32_t)(G * Cfg::STAGE_BYTES));
+          if (cta_rank == 0) mbar_arrive_expect_tx(fb_local, stage_tx);
           const uint32_t sA = tiles + stage * Cfg::STAGE_BYTES;
           const uint32_t sB = sA + Cfg::kSplit * Cfg::A_BYTES;
           const int k0 = p.debug_same_k ? 0 : kb * Cfg::BLOCK_K;
-          tma_load_3d<G>(sA, &tmA, fb, k0, m_row, b, p.hint_a);
+          tma_load_3d<G>(sA, mapA, fb, k0, m_row, b, p.hint_a);
           if constexpr (Cfg::kSplit == 2) tma_load_3d<G>(sA + Cfg::A_BYTES, &tmA_lo, fb, k0, m_row, b, p.hint_a);
           if constexpr (Cfg::kBKMajor) {
             tma_load_3d<G>(sB, &tmB, fb, k0, n_col, b, p.hint_b);
@@ -447,7 +469,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int acc = 0;
       uint32_t acc_phase = 0;
       TileSeq q{cluster_id, 0, 0u};
-      for (bool more = q.tile < p.num_tiles; more; more = next_tile(q, false)) {
+      for (bool more = q.tile < p.num_work; more; more = next_tile(q, false)) {
         if constexpr (Cfg::kMBlocks == 1) {
           // One accumulator per chunk of k-blocks (the whole K unless kChunkKB is set).
           const int chunk_kb = Cfg::kChunkKB > 0 ? Cfg::kChunkKB : p.num_kb;
@@ -468,6 +490,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               in_chunk = 0;
             }
           }
+        } else if (q.tile >= p.split_from) {
+          // Half tile: the X accumulator only.  Y is waited for as well (and released untouched by the epilogue), which
+          // keeps the two accumulators' phases in step with the whole tiles before and after.
+          const uint32_t dX = tmem_base;
+          mbar_wait<true>(tempty_bar, acc_phase ^ 1u);
+          mbar_wait<true>(tempty_bar + 8u, acc_phase ^ 1u);
+          tc_fence_after();
+          for (int kb = 0; kb < p.num_kb; ++kb) {
+            mbar_wait(full_bar + 8u * stage, phase);
+            tc_fence_after();
+            issue_kblock(stage, 0, dX, kb == 0);
+            umma_commit<G>(empty_bar + 8u * stage, kPairMask);
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          }
+          umma_commit<G>(tfull_bar, kPairMask);
+          acc_phase ^= 1u;
         } else {
           const uint32_t dX = tmem_base, dY = tmem_base + (uint32_t)Cfg::BLOCK_N;
           const int head = p.num_kb < Cfg::kStagger ? p.num_kb : Cfg::kStagger;
@@ -618,10 +656,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int acc = 0;
     uint32_t acc_phase = 0;
     TileSeq q{cluster_id, 0, 0u};
-    for (bool more = q.tile < p.num_tiles; more; more = next_tile(q, true)) {
-      int b, m_blk, n_blk;
-      decode_tile(p, q.tile, b, m_blk, n_blk);
-      const int row0 = m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M + quarter * 32;
+    for (bool more = q.tile < p.num_work; more; more = next_tile(q, true)) {
+      int b, m_blk, n_blk, half;
+      decode_tile(p, decode_work(p, q.tile, half), b, m_blk, n_blk);
+      const int row0 = (Cfg::kMBlocks == 2 && half >= 0)
+                           ? m_blk * Cfg::TILE_M + half * (Cfg::TILE_M / 2) + (int)cta_rank * (Cfg::CTA_M / 2) + quarter * 32
+                           : m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M + quarter * 32;
       const int col0 = n_blk * Cfg::BLOCK_N;
       const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
       if constexpr (Cfg::kChunkKB > 0) {
@@ -680,7 +720,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         mbar_wait(tfull_bar, acc_phase);
         tc_fence_after();
         drain(lane_base, row0, col0, b, 0);                                    // X: rows 0..127 of the slab
-        drain(lane_base + (uint32_t)Cfg::BLOCK_N, row0 + 128, col0, b, 1);     // Y: rows 128..255
+        if (half < 0) {
+          drain(lane_base + (uint32_t)Cfg::BLOCK_N, row0 + 128, col0, b, 1);   // Y: rows 128..255
+        } else if (lane == 0) {  // half tile: Y was not used, hand it straight back
+          if constexpr (G == 2) mbar_arrive_cluster(tempty_leader + 8u);
+          else mbar_arrive(tempty_bar + 8u);
+        }
         signal_band(b, m_blk);
         acc_phase ^= 1u;
       }

@@ -110,6 +110,29 @@ def test_every_kernel_variant_agrees(env, monkeypatch):
     assert torch.equal(b2.matmul(A, B), base)
 
 
+@pytest.mark.parametrize("dname", ["bfloat16", "float16"])
+def test_last_wave_in_half_tiles_gives_the_same_bits(dname, monkeypatch):
+    """Problems several waves long hand out their last tiles as half tiles (GemmParams::num_work): same arithmetic,
+    same bits as whole tiles — also with ragged edges, where a lower half may lie entirely outside the matrix —
+    and right against the oracle on rows from the split region and from the unsplit one."""
+    dt = DTYPES[dname]
+    torch.manual_seed(17)
+    for M, N, K in ((8192, 4864, 192), (8000, 4872, 328)):  # 16 x 19 = 304 tall tiles >= 4 x 74 clusters
+        A = torch.randn(M, K, dtype=dt, device=DEV)
+        B = torch.randn(K, N, dtype=dt, device=DEV)
+        monkeypatch.setenv("B2MM_SPLIT_TAIL", "1")
+        C = torch.full((M, N), 3.0, dtype=dt, device=DEV)
+        b2.matmul(A, B, out=C)
+        assert "half tiles" in _lib.load().b2mm_last_kernel().decode()
+        monkeypatch.setenv("B2MM_SPLIT_TAIL", "0")
+        C0 = b2.matmul(A, B)
+        assert "half tiles" not in _lib.load().b2mm_last_kernel().decode()
+        assert torch.equal(C, C0)
+        for r0 in (0, M - 300):
+            ref = oracle.gemm_block_f64(A, B, r0, 300, 0, N)
+            assert rel_err(C[r0:r0 + 300], ref) <= TOL[dt]
+
+
 def test_independent_recipe_on_device_matches_oracle():
     """benchmark_independent's recipe on the GPU generator (matmul_scaling_benchmark.py:73-75), rank 0 and 3."""
     for rank in (0, 3):

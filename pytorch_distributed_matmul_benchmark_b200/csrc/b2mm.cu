@@ -223,13 +223,17 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   if (sms <= 0) return fail(B2MM_ERR_CUDA, "cannot query SM count");
   if (max_sms > 0 && max_sms < sms) sms = max_sms;
   int clusters = sms / Cfg::kCtaGroup;
-  // Last wave at half-tile granularity (tall tiles, dynamic scheduler): with one tile per request the clusters finish
-  // spread over a whole tile period, so on average half a tile period of every SM is idle at the end (1.7 % of a
-  // 16384^3 GEMM); handing out the last `clusters` tiles as 2 x `clusters` half tiles halves that.  Only when the
-  // problem is several waves long, and not with progress counters (their targets count whole tiles).
+  // Last wave at half-tile granularity (tall tiles, dynamic scheduler; B2MM_SPLIT_TAIL=1, OFF by default): with one
+  // tile per request the clusters finish spread over a whole tile period, so on average half a tile period of every
+  // SM is idle at the end (1.7 % of a 16384^3 GEMM); handing out the last `clusters` tiles as 2 x `clusters` half
+  // tiles halves that idle time.  Measured (round 2, interleaved A/B in the sustained state): 1365 vs 1370 TFLOP/s
+  // at 16384^3, 1318 vs 1344 at 8192^3 — no gain, because under the 1 kW cap throughput is set by the energy per
+  // flop, not by SM occupancy (idle SMs give their power to the busy ones), and half tiles pull a third more bytes
+  // per flop from L2.  Kept for parts / runs that are not power limited.  Only when the problem is several waves
+  // long, and not with progress counters (their targets count whole tiles).
   p.split_from = p.num_tiles;
   if (Cfg::kMBlocks == 2 && Cfg::kSplit == 1 && p.dynamic && !o.band_counter && o.tiles_per_cluster == 0 &&
-      p.num_tiles >= 4 * clusters && env_int("B2MM_SPLIT_TAIL", 1))
+      p.num_tiles >= 4 * clusters && env_int("B2MM_SPLIT_TAIL", 0))
     p.split_from = p.num_tiles - clusters;
   p.num_work = p.split_from + 2 * (p.num_tiles - p.split_from);
   if (clusters > p.num_work || p.dynamic) clusters = p.num_work;

@@ -54,24 +54,46 @@ class _Blob:
         self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
 
 
+SOCKET_TIMEOUT_S = 60.0  # a peer that died before connecting must not leave the others waiting for ever
+
+
 def _send_fd_to_peers(fd: int, n_peers: int, path: str) -> None:
-    with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as srv:
-        srv.bind(path)
-        srv.listen(n_peers)
-        dist.barrier()  # peers connect only once the socket exists
-        for _ in range(n_peers):
-            conn, _ = srv.accept()
-            with conn:
-                socket.send_fds(conn, [b"m"], [fd])
-    os.unlink(path)
+    try:
+        with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as srv:
+            srv.settimeout(SOCKET_TIMEOUT_S)
+            srv.bind(path)
+            srv.listen(n_peers)
+            dist.barrier()  # peers connect only once the socket exists
+            for _ in range(n_peers):
+                conn, _ = srv.accept()
+                with conn:
+                    socket.send_fds(conn, [b"m"], [fd])
+    finally:
+        try:
+            os.unlink(path)
+        except OSError:
+            pass
 
 
 def _recv_fd(path: str) -> int:
     dist.barrier()
     with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+        c.settimeout(SOCKET_TIMEOUT_S)
         c.connect(path)
         _, fds, _, _ = socket.recv_fds(c, 1, 1)
+    if not fds:
+        raise RuntimeError("no file descriptor received for the multicast object")
     return fds[0]
+
+
+def _agree(phase: str, error) -> None:
+    """Collective end of a set-up phase: every rank reports its own outcome, and if ANY rank failed, EVERY rank raises
+    (the same message everywhere), so nobody is left waiting in the next barrier for a rank that has already given up."""
+    outcomes = [None] * dist.get_world_size()
+    dist.all_gather_object(outcomes, None if error is None else str(error))
+    failed = [(r, e) for r, e in enumerate(outcomes) if e is not None]
+    if failed:
+        raise RuntimeError(f"multicast set-up failed in phase '{phase}': " + "; ".join(f"rank {r}: {e}" for r, e in failed))
 
 
 class MulticastBuffer:
@@ -126,35 +148,61 @@ class MulticastBuffer:
                 payload = [os.path.join(tempfile.gettempdir(), f"b2mm_mc_{os.getpid()}_{id(self):x}.sock")]
             except RuntimeError as e:
                 payload = [f"ERROR: {e}"]
+                if getattr(self, "_mc", None) is not None:  # created but not exportable: do not leak the object
+                    drv.cuMemRelease(self._mc)
+                    self._mc = None
         dist.broadcast_object_list(payload, src=0)
         if payload[0].startswith("ERROR: "):
             self._closed = True
             raise RuntimeError(payload[0][len("ERROR: "):])
-        if rank == 0:
-            _send_fd_to_peers(fd, world_size - 1, payload[0])
-            os.close(fd)
-        else:
-            fd = _recv_fd(payload[0])
-            self._mc = _ok(drv.cuMemImportFromShareableHandle(fd, fd_type), "cuMemImportFromShareableHandle")
-            os.close(fd)
-        _ok(drv.cuMulticastAddDevice(self._mc, dev), "cuMulticastAddDevice")
-        dist.barrier()  # every device has been added before anybody binds memory
+        # From here on every phase ends in _agree(): a failure on one rank (import, out of memory, bind, a socket that
+        # timed out) makes all ranks unwind what they built and raise together; Communicator._try_multicast then takes
+        # the peer-mapped path on every rank.
+        self._mem = self._va = self._mc_va = None
+        self._bound = self._mapped = self._mc_mapped = False
+        err = None
+        try:
+            if rank == 0:
+                try:
+                    _send_fd_to_peers(fd, world_size - 1, payload[0])
+                finally:
+                    os.close(fd)
+            else:
+                fd = _recv_fd(payload[0])
+                try:
+                    self._mc = _ok(drv.cuMemImportFromShareableHandle(fd, fd_type), "cuMemImportFromShareableHandle")
+                finally:
+                    os.close(fd)
+            _ok(drv.cuMulticastAddDevice(self._mc, dev), "cuMulticastAddDevice")
+        except (RuntimeError, OSError) as e:
+            err = e
+        self._phase_end("hand-over of the multicast object / add device", err)  # every device added before anybody binds
 
         # this rank's physical memory, its ordinary mapping, and its binding into the multicast object
-        self._mem = _ok(drv.cuMemCreate(size, alloc, 0), "cuMemCreate")
-        self._va = _ok(drv.cuMemAddressReserve(size, gran, 0, 0), "cuMemAddressReserve")
-        _ok(drv.cuMemMap(self._va, size, 0, self._mem, 0), "cuMemMap")
         access = drv.CUmemAccessDesc()
         access.location.type = drv.CUmemLocationType.CU_MEM_LOCATION_TYPE_DEVICE
         access.location.id = index
         access.flags = drv.CUmemAccess_flags.CU_MEM_ACCESS_FLAGS_PROT_READWRITE
-        _ok(drv.cuMemSetAccess(self._va, size, [access], 1), "cuMemSetAccess")
-        _ok(drv.cuMulticastBindMem(self._mc, 0, self._mem, 0, size, 0), "cuMulticastBindMem")
-        dist.barrier()  # every rank's memory is bound before the multicast address is used
+        try:
+            self._mem = _ok(drv.cuMemCreate(size, alloc, 0), "cuMemCreate")
+            self._va = _ok(drv.cuMemAddressReserve(size, gran, 0, 0), "cuMemAddressReserve")
+            _ok(drv.cuMemMap(self._va, size, 0, self._mem, 0), "cuMemMap")
+            self._mapped = True
+            _ok(drv.cuMemSetAccess(self._va, size, [access], 1), "cuMemSetAccess")
+            _ok(drv.cuMulticastBindMem(self._mc, 0, self._mem, 0, size, 0), "cuMulticastBindMem")
+            self._bound = True
+        except RuntimeError as e:
+            err = e
+        self._phase_end("allocate / map / bind", err)  # every rank's memory is bound before the multicast address is used
 
-        self._mc_va = _ok(drv.cuMemAddressReserve(size, gran, 0, 0), "cuMemAddressReserve(multicast)")
-        _ok(drv.cuMemMap(self._mc_va, size, 0, self._mc, 0), "cuMemMap(multicast)")
-        _ok(drv.cuMemSetAccess(self._mc_va, size, [access], 1), "cuMemSetAccess(multicast)")
+        try:
+            self._mc_va = _ok(drv.cuMemAddressReserve(size, gran, 0, 0), "cuMemAddressReserve(multicast)")
+            _ok(drv.cuMemMap(self._mc_va, size, 0, self._mc, 0), "cuMemMap(multicast)")
+            self._mc_mapped = True
+            _ok(drv.cuMemSetAccess(self._mc_va, size, [access], 1), "cuMemSetAccess(multicast)")
+        except RuntimeError as e:
+            err = e
+        self._phase_end("map the multicast address", err)
 
         self.ptr, self.mc_ptr = int(self._va), int(self._mc_va)
         flat = torch.as_tensor(_Blob(self.ptr, nbytes), device=device)
@@ -162,6 +210,42 @@ class MulticastBuffer:
         self.local.zero_()
         torch.cuda.synchronize(device)
         dist.barrier()
+
+    def _phase_end(self, phase: str, error) -> None:
+        try:
+            _agree(phase, error)
+        except RuntimeError:
+            self._unwind()
+            raise
+
+    def _unwind(self) -> None:
+        """Give back whatever exists, newest first; driver errors here are ignored (we are already failing)."""
+        drv = _drv()
+        index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        steps = []
+        if self._mc_va is not None:
+            if self._mc_mapped:
+                steps.append(lambda: drv.cuMemUnmap(self._mc_va, self.size))
+            steps.append(lambda: drv.cuMemAddressFree(self._mc_va, self.size))
+        if self._bound:
+            steps.append(lambda: drv.cuMulticastUnbind(self._mc, drv.cuDeviceGet(index)[1], 0, self.size))
+        if self._va is not None:
+            if self._mapped:
+                steps.append(lambda: drv.cuMemUnmap(self._va, self.size))
+            steps.append(lambda: drv.cuMemAddressFree(self._va, self.size))
+        if self._mem is not None:
+            steps.append(lambda: drv.cuMemRelease(self._mem))
+        if getattr(self, "_mc", None) is not None:
+            steps.append(lambda: drv.cuMemRelease(self._mc))
+        for step in steps:
+            try:
+                step()
+            except Exception:
+                pass
+        self._mem = self._va = self._mc_va = self._mc = None
+        self._bound = self._mapped = self._mc_mapped = False
+        self.local = None
+        self._closed = True
 
     def close(self) -> None:
         if self._closed:

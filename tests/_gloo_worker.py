@@ -59,6 +59,21 @@ def main(out_dir: str):
     result["sum"] = hostlib.metric_all_reduce(float(rank + 1), device, "sum")
     result["avg"] = hostlib.metric_all_reduce(float(rank + 1), device, "avg")
 
+    # a parity verdict is collective: one rank over the bar makes EVERY rank raise (nobody walks on into a collective
+    # the failing rank never reaches), and a pass returns the worst error over ranks everywhere
+    real_stdout = sys.stdout
+    sys.stdout = open(os.devnull, "w")
+    try:
+        try:
+            hostlib.report_check(rank, 1.0 if rank == 1 else 0.0, 0.5, "collective verdict", device=device)
+            result["check_raised"] = False
+        except RuntimeError as e:
+            result["check_raised"] = "1.000e+00 > 5.0e-01" in str(e)
+        result["check_pass_value"] = hostlib.report_check(rank, 0.125 * (rank + 1), 0.5, "collective verdict", device=device)
+    finally:
+        sys.stdout.close()
+        sys.stdout = real_stdout
+
     # batch_parallel: after bmm + all_reduce every rank holds the sum over ranks of its peers' products
     N, dt = 48, torch.float32
     A, B = reference_port.batch_parallel_inputs(rank, ws, N, dt)

@@ -59,3 +59,50 @@ def test_nvls_opt_out(monkeypatch):
     assert ops.Communicator.nvls_available(c) is True
     c.world_size = 1
     assert ops.Communicator.nvls_available(c) is False
+
+
+def test_a_setup_phase_fails_on_every_rank_when_one_rank_failed(monkeypatch):
+    """multicast._agree: all ranks report their outcome; one failure anywhere raises everywhere, naming the rank."""
+    import pytest
+    from pytorch_distributed_matmul_benchmark_b200 import multicast
+
+    class FakeDist:
+        def __init__(self, others):
+            self.others = others
+
+        def get_world_size(self):
+            return len(self.others) + 1
+
+        def all_gather_object(self, out, mine):
+            out[:] = [mine] + self.others
+
+    monkeypatch.setattr(multicast, "dist", FakeDist([None, None]))
+    multicast._agree("bind", None)  # everybody fine: no exception
+    monkeypatch.setattr(multicast, "dist", FakeDist([None, "cuMemCreate failed: CUDA_ERROR_OUT_OF_MEMORY (2)"]))
+    with pytest.raises(RuntimeError, match=r"phase 'bind'.*rank 2: cuMemCreate failed"):
+        multicast._agree("bind", None)  # THIS rank succeeded and still raises
+    with pytest.raises(RuntimeError, match="rank 0: boom"):
+        multicast._agree("bind", RuntimeError("boom"))
+
+
+def test_unwind_releases_what_was_built_newest_first(monkeypatch):
+    from pytorch_distributed_matmul_benchmark_b200 import multicast
+    log = []
+
+    class FakeDrv:
+        def __getattr__(self, name):
+            def call(*a):
+                log.append(name)
+                return (0, 0)
+            return call
+
+    monkeypatch.setattr(multicast, "_drv", lambda: FakeDrv())
+    b = multicast.MulticastBuffer.__new__(multicast.MulticastBuffer)
+    b.device, b.size = torch.device("cpu"), 4096
+    monkeypatch.setattr(torch.cuda, "current_device", lambda: 0)
+    b._mc, b._mem, b._va, b._mc_va = 11, 22, 33, None  # failed while mapping the multicast address was never reached
+    b._bound, b._mapped, b._mc_mapped = True, True, False
+    b._unwind()
+    assert log == ["cuDeviceGet", "cuMulticastUnbind", "cuMemUnmap", "cuMemAddressFree", "cuMemRelease", "cuMemRelease"]
+    assert b._closed and b._mc is None and b.local is None
+    b.close()  # a closed buffer's close() is a no-op

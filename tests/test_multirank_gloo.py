@@ -37,6 +37,8 @@ def test_collectives_and_aggregation(gloo_run):
         assert r["sum"] == pytest.approx(3.0) and r["avg"] == pytest.approx(1.5)
         assert r["batch_parallel_err"] < 1e-5
         assert r["matrix_parallel_err"] < 1e-5
+        assert r["check_raised"] is True, "a parity miss on rank 1 must raise on every rank"
+        assert r["check_pass_value"] == pytest.approx(0.25)  # MAX over ranks, the same on both
 
 
 def test_report_for_two_ranks(gloo_run):

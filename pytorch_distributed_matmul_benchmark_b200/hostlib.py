@@ -227,3 +227,37 @@ def parity_error(C: torch.Tensor, A: torch.Tensor, B: torch.Tensor, rows: int = 
     got = C.index_select(-2, idx).double()
     rms = ref.pow(2).mean().sqrt()
     return ((got - ref).abs() / (ref.abs() + rms)).max().item()
+
+
+def reduction_pair_error(got: torch.Tensor, ref: torch.Tensor, term_mag: torch.Tensor, world_size: int,
+                         chunk_rows: int = 2048) -> float:
+    """Two all_reduce(SUM) results of the same per-rank products, compared in units of the dtype's tolerance.
+
+    `ref` is the NCCL result (one rounding in the switch, or one per ring / tree step — each of a PARTIAL sum, which
+    can be far larger than the final, possibly cancelled, sum), `got` the library's own reduction (fp32 adds, one
+    rounding).  `term_mag` = sum over ranks of |T_r| + rms(T_r) bounds every partial sum, so two correct results obey
+        |got - ref| <= tol * ((world - 1) * term_mag + 2 * (|ref| + rms(ref)))      element by element;
+    the returned value is the largest ratio of the left side to the bracket (float64, chunked, on the device).
+    A flat bar against |ref| + rms(ref) alone is wrong for world > 2: measured at 4 GPUs, NCCL's tree result sits
+    3.4 such "ulps" from the exactly rounded sum where a term is large and the sum is not."""
+    g2, r2, m2 = (t.reshape(-1, t.shape[-1]) for t in (got, ref, term_mag))
+    sq = 0.0
+    for i in range(0, r2.shape[0], chunk_rows):
+        sq += r2[i:i + chunk_rows].double().pow(2).sum().item()
+    rms = (sq / max(r2.numel(), 1)) ** 0.5
+    worst = 0.0
+    for i in range(0, r2.shape[0], chunk_rows):
+        r = r2[i:i + chunk_rows].double()
+        bound = max(world_size - 1, 1) * m2[i:i + chunk_rows].double() + 2.0 * (r.abs() + rms)
+        worst = max(worst, ((g2[i:i + chunk_rows].double() - r).abs() / bound).max().item())
+    return worst
+
+
+def term_magnitudes(products) -> torch.Tensor:
+    """sum_r (|T_r| + rms(T_r)) in float32 for an iterable of per-rank products (consumed one at a time)."""
+    mag = None
+    for T in products:
+        t = T.float()
+        m = t.abs() + t.pow(2).mean().sqrt()
+        mag = m if mag is None else mag.add_(m)
+    return mag

@@ -91,7 +91,7 @@ def benchmark_data_parallel(matrix_size: int, dtype: torch.dtype, device: str, r
     avg_comm = (comm_ms / 1000.0) / max(num_iterations, 1)
     if check and comm_on:
         from .matmul_overlap_benchmark import _check_reduced_product
-        _check_reduced_product(ops, lambda: ops.all_reduce(C), C, matrix_size, dtype, device, rank)
+        _check_reduced_product(ops, lambda: ops.all_reduce(C), C, matrix_size, dtype, device, rank, ring=True)
     elif check:
         ops.matmul(A, B, out=C)
         _report_check(rank, hostlib.parity_error(C, A, B), hostlib.CHECK_TOL[dtype])

@@ -78,27 +78,29 @@ def benchmark_no_overlap(matrix_size: int, dtype: torch.dtype, device: str, rank
     avg_time = (start.elapsed_time(end) / 1000.0) / max(num_iterations, 1)
     if check and comm_on:
         # NCCL: one rounding inside the switch (NVLS) or one per ring step
-        _check_reduced_product(ops, lambda: ops.all_reduce(C), C, matrix_size, dtype, device, rank,
-                               roundings=max(dist.get_world_size() - 1, 2))
+        _check_reduced_product(ops, lambda: ops.all_reduce(C), C, matrix_size, dtype, device, rank, ring=True)
     return avg_time, _compute_only_tflops(ops, A, B, C, matrix_size), 0.0
 
 
 def _check_reduced_product(ops: hostlib.Ops, reduce_fn, out: torch.Tensor, matrix_size: int, dtype: torch.dtype,
-                           device: str, rank: int, roundings: int = 2) -> None:
+                           device: str, rank: int, roundings: int = 2, ring: bool = False) -> None:
     """--check: every rank multiplies matrices seeded by its rank, reduces, and compares with the sum of all ranks'
     products recomputed locally (the reference reduces the rounded C tensors, so does the expectation).
 
     `roundings`: output-ulp budget of the reduction under test.  The library's own reductions add in fp32 and round
     ONCE whatever the world size; the NVSwitch (measured) truncates instead of rounding to nearest, so that one
-    rounding may cost a full ulp: 2 x tolerance.  Only the NCCL arm of `no_overlap` may round once per ring step."""
+    rounding may cost a full ulp: 2 x tolerance.  `ring`: the NCCL arm of `no_overlap`, which may round once per ring /
+    tree step — each a PARTIAL sum, bounded by the ranks' terms: hostlib.reduction_pair_error is the bar there."""
     world = dist.get_world_size() if dist.is_initialized() else 1
-    want = None
+    want = mag = None
     for r in range(world):
         torch.manual_seed(4000 + r)
         Ar = torch.randn(matrix_size, matrix_size, dtype=dtype, device=device)
         Br = torch.randn(matrix_size, matrix_size, dtype=dtype, device=device)
         Cr = ops.matmul(Ar, Br)
         want = Cr.double() if want is None else want + Cr.double()
+        m = hostlib.term_magnitudes([Cr])
+        mag = m if mag is None else mag + m
         if r == rank:
             out.copy_(Cr)
     ops.synchronize()
@@ -106,6 +108,11 @@ def _check_reduced_product(ops: hostlib.Ops, reduce_fn, out: torch.Tensor, matri
         dist.barrier()
     reduce_fn()
     ops.synchronize()
+    if ring:
+        # NCCL rounds partial sums, which the ranks' terms bound (not the final, possibly cancelled, sum)
+        err = hostlib.reduction_pair_error(out, want, mag, world)
+        hostlib.report_check(rank, err, hostlib.CHECK_TOL[dtype], "of the reduced product vs float64 sum", indent="  ", device=device)
+        return
     rms = want.pow(2).mean().sqrt()
     err = ((out.double() - want).abs() / (want.abs() + rms)).max().item()
     hostlib.report_check(rank, err, hostlib.CHECK_TOL[dtype] * roundings, "of the reduced product vs float64 sum", indent="  ",

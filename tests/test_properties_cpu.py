@@ -72,3 +72,25 @@ def test_oracle_is_exact_products_double_sum_one_rounding(M, N, K, seed):
         # and the float64 block the GPU tests compare against is that same product
         blk = oracle.gemm_block_f64(A, B, 0, M, 0, N).numpy()
         assert np.allclose(blk, ref64, rtol=1e-13, atol=1e-13)
+
+
+def test_two_correct_reductions_pass_the_pair_bound_and_a_wrong_one_does_not():
+    """hostlib.reduction_pair_error: a tree of bf16 adds (what NCCL may do) and an fp32 sum rounded once (what the
+    library's own reductions do) are both correct and must agree within the tolerance, for every world size, although
+    a flat bar against the final sum does not hold; a result that lost one rank's contribution must not pass."""
+    import torch
+    from pytorch_distributed_matmul_benchmark_b200 import hostlib
+    tol = hostlib.CHECK_TOL[torch.bfloat16]
+    torch.manual_seed(5)
+    for world in (2, 4, 8):
+        terms = [(torch.randn(256, 384) * 128).to(torch.bfloat16) for _ in range(world)]
+        level = list(terms)
+        while len(level) > 1:  # pairwise tree, every partial sum rounded to bf16
+            level = [level[i] + level[i + 1] for i in range(0, len(level), 2)]
+        tree = level[0]
+        once = sum(t.float() for t in terms).to(torch.bfloat16)
+        mag = hostlib.term_magnitudes(iter(terms))
+        assert mag.dtype == torch.float32 and mag.shape == tree.shape
+        assert hostlib.reduction_pair_error(once, tree, mag, world) <= tol
+        lost = (sum(t.float() for t in terms[1:])).to(torch.bfloat16)  # rank 0's product never arrived
+        assert hostlib.reduction_pair_error(lost, tree, mag, world) > tol

@@ -15,6 +15,7 @@ except Exception as e:
     print("no line:", e)
 PY
 tail -3 gpurun_out/r2h_bench_n4.err
+B2MM_NVLS=0 timeout 600 $TR --master-port 29616 bench.py --gpus 4 --steps 5 --warmup 3 2>/dev/null | python -c "import sys,json; d=json.loads([l for l in sys.stdin if l.startswith(chr(123))][-1]); print(\"NVLS=0 bench:\", d.get(\"modes_parity_ok\"), [(m[\"variant\"][:14], round(m[\"ms\"],3), m[\"parity_ok\"]) for m in d[\"modes\"]])"
 timeout 600 $TR --master-port 29612 matmul_scaling_benchmark.py --mode batch_parallel --fused --panels 2 --check --sizes 2048 4096 --iterations 5 --warmup 2 2>&1 | grep -E "Parity|ERROR|Fused" 
 timeout 600 $TR --master-port 29613 matmul_overlap_benchmark.py --mode no_overlap --check --sizes 2048 4096 --iterations 5 --warmup 2 2>&1 | grep -E "Parity|ERROR"
 timeout 600 $TR --master-port 29614 matmul_overlap_benchmark.py --mode overlap --check --sizes 2048 --iterations 5 --warmup 2 2>&1 | grep -E "Parity|ERROR"

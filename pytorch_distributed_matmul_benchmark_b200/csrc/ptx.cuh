@@ -148,26 +148,6 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const CUtensorMap
   }
 }
 
-// Same, delivered to the same smem offset of every CTA in `cta_mask`.
-template <int kCtaGroup>
-__device__ __forceinline__ void tma_load_3d_mcast(uint32_t dst_smem, const CUtensorMap* map, uint32_t mbar,
-                                                  int c0, int c1, int c2, uint16_t cta_mask,
-                                                  uint64_t cache_hint) {
-  if constexpr (kCtaGroup == 2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint"
-        " [%0], [%1, {%4, %5, %6}], [%2], %3, %7;"
-        ::"r"(dst_smem), "l"(map), "r"(mbar), "h"(cta_mask), "r"(c0), "r"(c1), "r"(c2), "l"(cache_hint)
-        : "memory");
-  } else {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint"
-        " [%0], [%1, {%4, %5, %6}], [%2], %3, %7;"
-        ::"r"(dst_smem), "l"(map), "r"(mbar), "h"(cta_mask), "r"(c0), "r"(c1), "r"(c2), "l"(cache_hint)
-        : "memory");
-  }
-}
-
 // shared -> global, 3-D tile, tracked by the issuing thread's bulk async-group.
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src_smem, int c0, int c1,
                                              int c2) {

@@ -51,3 +51,17 @@ def test_product_has_no_library_gemm_fallback():
             text = open(path).read()
             # comments may quote the library's measured numbers; what must not appear is a use of it
             assert not re.search(r"#include\s*[<\"]cublas|cublas(Lt)?[A-Z]\w*\s*\(|-lcublas|libcublas", text), path
+
+
+def test_tma_loads_are_never_multicast():
+    """TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+    memory hung the GPU.  The library's loads (operands A and B, always local) are plain per-CTA loads, so the rule
+    holds by construction: no `cp.async.bulk` load with `.multicast::cluster` exists in the sources or in the SASS."""
+    import subprocess
+    from pytorch_distributed_matmul_benchmark_b200 import _lib
+    for path in _files():
+        if path.endswith((".cu", ".cuh")):
+            for line in open(path).read().splitlines():
+                assert not ("cp.async.bulk" in line and "multicast::cluster" in line), path
+    sass = subprocess.check_output(["cuobjdump", "-sass", _lib.LIB_PATH], text=True, stderr=subprocess.DEVNULL)
+    assert not re.search(r"(UTMALDG|UBLKCP)\S*MULTICAST", sass)

@@ -497,7 +497,9 @@ def sharded_modes(args, rank: int, world: int, dev, t_independent_ms: float) -> 
     f_med = statistics.median(f for _, f in rounds)
     # the store path on its own: the same kernel with K = 64 has (almost) no math left, so its time is what the epilogue's
     # stores need to put all N x N outputs into every rank's buffer over NVLink — the measured link floor of this mode
-    store_only = timed(lambda: comm.matmul_allgather_fused(A[:, :64], B_local[:64], gbuf), warm=2)
+    A64, B64 = A[:, :64].contiguous(), B_local[:64].contiguous()  # the fused entry points take densely packed operands
+    store_only = timed(lambda: comm.matmul_allgather_fused(A64, B64, gbuf), warm=2)
+    del A64, B64
     comm.matmul_allgather_fused(A, B_local, gbuf)  # leave the real product in the buffer
     recs.append(dict(mode="matrix_parallel", variant="fused (GEMM epilogue stores each tile " + ("through ONE multicast TMA store, replicated by the NVSwitch"
                      if mc_gather else "into every rank's buffer by peer TMA stores") + "; + barrier)", ms=f_med, gemm_alone_ms=g_med,

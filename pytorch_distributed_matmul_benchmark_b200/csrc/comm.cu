@@ -317,6 +317,7 @@ int b2mm_gemm_allgather_fused(const void* A, const void* B_local, void* const* p
   GemmOpts opts;
   opts.fan_ptrs = dst;
   opts.fanout = world;
+  opts.head_split = world > 4;  // only where the stores, not the math, bound the step (measured: -2.7 % at 8 GPUs, +2.5 % at 2)
   return gemm_impl(A, B_local, nullptr, M, n_local, K, K, n_local, n_local, 1, 0, 0, 0, dtype, workspace, workspace_bytes,
                    (cudaStream_t)stream, opts);
 }
@@ -333,6 +334,7 @@ int b2mm_gemm_allgather_nvls(const void* A, const void* B_local, void* slabs_mul
   GemmOpts opts;
   opts.fan_ptrs = dst;
   opts.fanout = 1;
+  opts.head_split = world > 4;  // only where the stores, not the math, bound the step (measured: -2.7 % at 8 GPUs, +2.5 % at 2)
   return gemm_impl(A, B_local, nullptr, M, n_local, K, K, n_local, n_local, 1, 0, 0, 0, dtype, workspace, workspace_bytes,
                    (cudaStream_t)stream, opts);
 }

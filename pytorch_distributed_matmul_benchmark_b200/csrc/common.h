@@ -22,6 +22,7 @@ struct GemmOpts {
   int tiles_per_cluster = 0;          // dynamic scheduler: clusters retire after this many tiles (0 = never)
   int* band_counter = nullptr;        // progress counters, one per band of `band_rows` rows (see GemmParams)
   int band_rows = 0;
+  bool head_split = false;            // hand out the first wave as half-width items (fused gather: earlier first stores)
   // out: filled by gemm_impl when band_counter is set
   mutable int signals_per_band = 0;   // value a band's counter reaches when the band is complete
   mutable int bands_per_batch = 0;

@@ -70,8 +70,14 @@ struct GemmParams {
   // Work items handed out by the scheduler.  Items [0, split_from) are whole tiles; every later pair of items is the
   // upper and lower half (CTA_M / 2 rows per CTA, the X accumulator only) of one of the last tiles, so that the
   // final wave is balanced at half-tile granularity (kMBlocks == 2 only; split_from == num_tiles: no halves).
-  int num_work;          // split_from + 2 * (num_tiles - split_from)
+  int num_work;          // split_from + 2 * (num_tiles - split_from)   (+ head_tiles)
   int split_from;
+  // kMBlocks == 1, BLOCK_N == 256 only: the FIRST head_tiles tiles are handed out as 2 x head_tiles half-width items
+  // (128 columns each, MMA N = 128 through idesc_half), so that the first finished outputs exist after half a tile
+  // period.  Used by the fused gather, whose stores are the bottleneck and cannot start before the first tiles have
+  // run through all of K.  0: off.
+  int head_tiles;
+  uint32_t idesc_half;   // instruction descriptor with N = BLOCK_N / 2
   int num_kb;            // ceil(K / BLOCK_K)
   int group_m;           // tile-rasterisation group height (in tiles)
   uint32_t idesc;        // tcgen05 instruction descriptor
@@ -245,6 +251,14 @@ __device__ __forceinline__ void decode_tile(const GemmParams& p, int tile, int& 
 
 // Work item -> tile index and which part of it: -1 = the whole tile, 0 / 1 = its upper / lower half.
 __device__ __forceinline__ int decode_work(const GemmParams& p, int work, int& half) {
+  if (p.head_tiles > 0) {  // half = 2 / 3: the left / right half (in N) of one of the first tiles
+    if (work < 2 * p.head_tiles) {
+      half = 2 + (work & 1);
+      return work >> 1;
+    }
+    half = -1;
+    return work - p.head_tiles;
+  }
   if (work < p.split_from) {
     half = -1;
     return work;
@@ -390,9 +404,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const bool is_half = Cfg::kMBlocks == 2 && half >= 0;
         const int m_row = is_half ? m_blk * Cfg::TILE_M + half * (Cfg::TILE_M / 2) + (int)cta_rank * (Cfg::CTA_M / 2)
                                   : m_blk * Cfg::TILE_M + (int)cta_rank * Cfg::CTA_M;
-        const uint32_t stage_tx = (uint32_t)(G * (is_half ? Cfg::STAGE_BYTES - Cfg::kSplit * Cfg::A_BYTES / 2 : Cfg::STAGE_BYTES));
+        const bool n_half = Cfg::kMBlocks == 1 && half >= 2;  // half-width item: this CTA loads LOAD_N / 2 columns of B
+        const uint32_t stage_tx = (uint32_t)(G * (is_half ? Cfg::STAGE_BYTES - Cfg::kSplit * Cfg::A_BYTES / 2
+                                                 : n_half ? Cfg::STAGE_BYTES - Cfg::kSplit * Cfg::B_BYTES / 2 : Cfg::STAGE_BYTES));
         const CUtensorMap* mapA = is_half ? &tmA_lo : &tmA;
-        const int n_col = n_blk * Cfg::BLOCK_N + (int)cta_rank * Cfg::LOAD_N;
+        const int n_col = n_half ? n_blk * Cfg::BLOCK_N + (half - 2) * (Cfg::BLOCK_N / 2) + (int)cta_rank * (Cfg::LOAD_N / 2)
+                                 : n_blk * Cfg::BLOCK_N + (int)cta_rank * Cfg::LOAD_N;
+        const int b_chunks = n_half ? Cfg::B_CHUNKS / 2 : Cfg::B_CHUNKS;
         if (p.trace) {  // row 0: SM id of each CTA; row 1 + i: start time of its i-th tile
           unsigned long long now;
           asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
@@ -418,6 +436,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           } else {
 #pragma unroll
             for (int c = 0; c < Cfg::B_CHUNKS; ++c) {
+              if (c >= b_chunks) break;
               tma_load_3d<G>(sB + c * Cfg::B_CHUNK_BYTES, &tmB, fb, n_col + c * Cfg::N_ATOM, k0, b, p.hint_b);
               if constexpr (Cfg::kSplit == 2)
                 tma_load_3d<G>(sB + Cfg::B_BYTES + c * Cfg::B_CHUNK_BYTES, &tmB_lo, fb, n_col + c * Cfg::N_ATOM, k0, b,
@@ -451,6 +470,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       constexpr uint32_t A_MBLOCK = (128 * Cfg::kSwz) >> 4;               // next 128 rows of A in the stage
 
       // All MMAs of one k-block for accumulator block `mb` (rows mb*128.. of this CTA's A slab).
+      uint32_t idesc = p.idesc;  // switched to idesc_half for the half-width items of the first wave
       auto issue_kblock = [&](int stage, int mb, uint32_t d_tmem, bool first_kb) {
         const uint32_t soff = (uint32_t)(stage * Cfg::STAGE_BYTES) >> 4;
         const uint64_t a_hi = a_desc0 + soff + (uint32_t)mb * A_MBLOCK;
@@ -461,11 +481,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if constexpr (Cfg::kSplit == 2) {
             const uint64_t a_lo = a_hi + (Cfg::A_BYTES >> 4);
             const uint64_t b_lo = b_hi + (Cfg::B_BYTES >> 4);
-            umma<G, Cfg::kTf32>(d_tmem, a_lo + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, acc_in);
-            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_lo + k * B_KSTEP, p.idesc, 1u);
-            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, 1u);
+            umma<G, Cfg::kTf32>(d_tmem, a_lo + k * A_KSTEP, b_hi + k * B_KSTEP, idesc, acc_in);
+            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_lo + k * B_KSTEP, idesc, 1u);
+            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, idesc, 1u);
           } else {
-            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, p.idesc, acc_in);
+            umma<G, Cfg::kTf32>(d_tmem, a_hi + k * A_KSTEP, b_hi + k * B_KSTEP, idesc, acc_in);
           }
         }
       };
@@ -477,6 +497,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       TileSeq q{cluster_id, 0, 0u};
       for (bool more = q.tile < p.num_work; more; more = next_tile(q, false)) {
         if constexpr (Cfg::kMBlocks == 1) {
+          idesc = (p.head_tiles > 0 && q.tile < 2 * p.head_tiles) ? p.idesc_half : p.idesc;
           // One accumulator per chunk of k-blocks (the whole K unless kChunkKB is set).
           const int chunk_kb = Cfg::kChunkKB > 0 ? Cfg::kChunkKB : p.num_kb;
           int in_chunk = 0;
@@ -609,9 +630,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
     // Move this warp's 32 rows of one accumulator (BLOCK_N columns at t_acc) to C, 128 bytes
     // per row at a time; hand the accumulator back (slot) as soon as it has been read.
-    auto drain = [&](uint32_t t_acc, int row0, int col0, int b, int slot) {
+    auto drain = [&](uint32_t t_acc, int row0, int col0, int b, int slot, int n_chunks) {
 #pragma unroll 1
-      for (int c = 0; c < Cfg::OUT_CHUNKS; ++c) {
+      for (int c = 0; c < n_chunks; ++c) {
         const uint32_t sbuf = my_stage + buf * Cfg::OUT_BUF_BYTES;
         // the TMA store issued two chunks ago must have finished reading this buffer
         if (lane == 0) tma_store_wait_read<1>();
@@ -643,7 +664,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           for (int j = 0; j < 8; ++j)
             st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), v0[4 * j + 0], v0[4 * j + 1], v0[4 * j + 2], v0[4 * j + 3]);
         }
-        if (c == Cfg::OUT_CHUNKS - 1) {
+        if (c == n_chunks - 1) {
           // all of this warp's TMEM reads of the accumulator are done: hand it back
           tc_fence_before();
           __syncwarp();
@@ -719,15 +740,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       } else if constexpr (Cfg::kMBlocks == 1) {
         mbar_wait(tfull_bar + 8u * acc, acc_phase);
         tc_fence_after();
-        drain(lane_base + (uint32_t)(acc * Cfg::BLOCK_N), row0, col0, b, acc);
+        if (half >= 2)  // half-width item of the first wave: 128 columns, at the left or right half of the tile
+          drain(lane_base + (uint32_t)(acc * Cfg::BLOCK_N), row0, col0 + (half - 2) * (Cfg::BLOCK_N / 2), b, acc, Cfg::OUT_CHUNKS / 2);
+        else
+          drain(lane_base + (uint32_t)(acc * Cfg::BLOCK_N), row0, col0, b, acc, Cfg::OUT_CHUNKS);
         signal_band(b, m_blk);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       } else {
         mbar_wait(tfull_bar, acc_phase);
         tc_fence_after();
-        drain(lane_base, row0, col0, b, 0);                                    // X: rows 0..127 of the slab
+        drain(lane_base, row0, col0, b, 0, Cfg::OUT_CHUNKS);                   // X: rows 0..127 of the slab
         if (half < 0) {
-          drain(lane_base + (uint32_t)Cfg::BLOCK_N, row0 + 128, col0, b, 1);   // Y: rows 128..255
+          drain(lane_base + (uint32_t)Cfg::BLOCK_N, row0 + 128, col0, b, 1, Cfg::OUT_CHUNKS);  // Y: rows 128..255
         } else if (lane == 0) {  // half tile: Y was not used, hand it straight back
           if constexpr (G == 2) mbar_arrive_cluster(tempty_leader + 8u);
           else mbar_arrive(tempty_bar + 8u);

@@ -133,6 +133,29 @@ def test_last_wave_in_half_tiles_gives_the_same_bits(dname, monkeypatch):
             assert rel_err(C[r0:r0 + 300], ref) <= TOL[dt]
 
 
+@pytest.mark.parametrize("dname", ["bfloat16", "float16"])
+def test_first_wave_in_half_width_items_gives_the_same_bits(dname, monkeypatch):
+    """The fused gather hands out its first wave as half-width items (GemmParams::head_tiles) so that its stores start
+    earlier; forced here on a plain GEMM (B2MM_SPLIT_HEAD=1 with the 256x256 tiles it applies to): same bits as whole
+    tiles, also where the right half of an edge tile lies almost or entirely outside the matrix."""
+    dt = DTYPES[dname]
+    torch.manual_seed(19)
+    monkeypatch.setenv("B2MM_M_BLOCKS", "1")
+    monkeypatch.setenv("B2MM_BLOCK_N", "256")
+    for M, N, K in ((4096, 2560, 320), (4000, 2440, 136), (4096, 2312, 72)):  # >= 148 tiles of 256 x 256
+        A = torch.randn(M, K, dtype=dt, device=DEV)
+        B = torch.randn(K, N, dtype=dt, device=DEV)
+        monkeypatch.setenv("B2MM_SPLIT_HEAD", "0")
+        C0 = b2.matmul(A, B)
+        assert "half-width" not in _lib.load().b2mm_last_kernel().decode()
+        monkeypatch.setenv("B2MM_SPLIT_HEAD", "1")
+        C = torch.full((M, N), 5.0, dtype=dt, device=DEV)
+        b2.matmul(A, B, out=C)
+        assert "first wave in half-width items" in _lib.load().b2mm_last_kernel().decode()
+        assert torch.equal(C, C0)
+        assert rel_err(C[:300], oracle.gemm_block_f64(A, B, 0, 300, 0, N)) <= TOL[dt]
+
+
 def test_fp32_with_64_byte_k_blocks_gives_the_same_bits(monkeypatch):
     """B2MM_FP32_K16=1 runs the 3xTF32 kernel on SWIZZLE_64B tiles (k-blocks of 16): the same sums in the same order."""
     torch.manual_seed(23)

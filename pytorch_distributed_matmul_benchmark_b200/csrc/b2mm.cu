@@ -209,12 +209,25 @@ static int launch_cfg(const Operands& o, int max_sms, cudaStream_t stream) {
   p.band_counter = o.band_counter;
   p.band_tiles = 1;
   p.bands_per_batch = 1;
+  p.fine_from = p.m_tiles;
   if (o.band_counter) {
     if (o.band_rows % Cfg::TILE_M) return fail(B2MM_ERR_UNSUPPORTED, "band of %d rows is not a whole number of %d-row tiles", o.band_rows, Cfg::TILE_M);
     p.band_tiles = o.band_rows / Cfg::TILE_M;
     p.bands_per_batch = (p.m_tiles + p.band_tiles - 1) / p.band_tiles;
     p.group_m = p.band_tiles;  // the raster band IS the signalling band: bands complete in order
     o.opts->signals_per_band = p.band_tiles * p.n_tiles * Cfg::kCtaGroup * Cfg::kEpiWarps;
+    // The reduction of the LAST band is the one nothing hides: B2MM_FINE_TAIL=1 splits that band into bands of one
+    // tile row (when the rows divide evenly and the caller allows it).  OFF by default: parity-tested on 2 GPUs, but
+    // the 8-GPU A/B was within the noise (6.67 / 6.72 ms without, 6.70 / 6.47 with), so the proven geometry stays.
+    o.opts->fine_bands = 0;
+    if (o.opts->fine_tail_ok && p.band_tiles > 1 && p.m_tiles % p.band_tiles == 0 && p.m_tiles >= 2 * p.band_tiles &&
+        o.M % Cfg::TILE_M == 0 && env_int("B2MM_FINE_TAIL", 0)) {
+      p.fine_from = p.m_tiles - p.band_tiles;
+      p.bands_per_batch += p.band_tiles - 1;
+      o.opts->fine_bands = p.band_tiles;
+      o.opts->fine_rows = Cfg::TILE_M;
+      o.opts->signals_per_fine_band = p.n_tiles * Cfg::kCtaGroup * Cfg::kEpiWarps;
+    }
     o.opts->bands_per_batch = p.bands_per_batch;
   }
   // Dynamic (hardware work-stealing) scheduling unless the caller capped the SMs.

@@ -597,23 +597,33 @@ static int gemm_allreduce_fused_impl(Comm* c, const void* A, const void* B, void
   prefer_gemm_carveout();
   // compute: clear the progress counters, then ONE GEMM over the whole batch on the whole device; its
   // epilogues count finished tiles per row band.
-  const int total_bands = (int)(n_bands * local_batch);
-  if (cudaMemsetAsync(band_counters, 0, sizeof(int) * total_bands, compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "memset failed");
+  // (the caller's counter array holds at least 256 ints: room for kMaxPanels bands however the last one is split)
+  if (cudaMemsetAsync(band_counters, 0, sizeof(int) * 4 * kMaxPanels, compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "memset failed");
   if (cudaEventRecord(c->panel_done[0], compute) != cudaSuccess) return fail(B2MM_ERR_CUDA, "event record failed");
   if (cudaStreamWaitEvent(cs, c->panel_done[0], 0) != cudaSuccess) return fail(B2MM_ERR_CUDA, "stream wait failed");
   GemmOpts opts;
   opts.band_counter = band_counters;
   opts.band_rows = (int)band_rows;
+  opts.fine_tail_ok = true;
   int rc = gemm_impl(A, B, C_local, N, N, N, N, N, N, local_batch, N * N, N * N, N * N, dtype, workspace, workspace_bytes,
                      compute, opts);
   if (rc) return rc;
-  if (opts.bands_per_batch != n_bands) return fail(B2MM_ERR_UNSUPPORTED, "band geometry mismatch (%d vs %d)", opts.bands_per_batch, n_bands);
+  // The GEMM may have split the last band into `fine_bands` bands of one tile row: the reduction that nothing hides
+  // (the one of the rows finished last) is then a fraction of a band.
+  const int coarse = opts.fine_bands > 0 ? n_bands - 1 : n_bands;
+  const int per_batch = coarse + opts.fine_bands;
+  if (opts.bands_per_batch != per_batch || per_batch * local_batch > 4 * kMaxPanels)
+    return fail(B2MM_ERR_UNSUPPORTED, "band geometry mismatch (%d vs %d)", opts.bands_per_batch, per_batch);
+  if (opts.fine_bands > 0 && ((int64_t)opts.fine_rows * N * es) % (16 * c->world))
+    return fail(B2MM_ERR_UNSUPPORTED, "fine band size is not a multiple of 16 bytes x world");
   // comm: one reduction per band, queued now, each waiting (on the device) for its band, then for its peers.
   for (int64_t b = 0; b < local_batch; ++b) {
-    for (int i = 0; i < n_bands; ++i) {
-      const int64_t elem_off = b * N * N + (int64_t)i * band_rows * N;
-      if ((rc = launch_sync_reduce(c, pp, sp, elem_off, band_rows * N, dtype, band_counters + b * n_bands + i,
-                                   opts.signals_per_band, cs, mc)))
+    for (int i = 0; i < per_batch; ++i) {
+      const bool fine = i >= coarse;
+      const int64_t row0 = fine ? (int64_t)coarse * band_rows + (int64_t)(i - coarse) * opts.fine_rows : (int64_t)i * band_rows;
+      const int64_t rows = fine ? opts.fine_rows : band_rows;
+      if ((rc = launch_sync_reduce(c, pp, sp, b * N * N + row0 * N, rows * N, dtype, band_counters + b * per_batch + i,
+                                   fine ? opts.signals_per_fine_band : opts.signals_per_band, cs, mc)))
         return rc;
     }
   }

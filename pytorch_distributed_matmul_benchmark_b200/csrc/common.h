@@ -24,8 +24,12 @@ struct GemmOpts {
   int band_rows = 0;
   bool head_split = false;            // hand out the first wave as half-width items (fused gather: earlier first stores)
   // out: filled by gemm_impl when band_counter is set
+  bool fine_tail_ok = false;          // the caller can handle a last band split into one-tile-row bands (see out fields)
   mutable int signals_per_band = 0;   // value a band's counter reaches when the band is complete
-  mutable int bands_per_batch = 0;
+  mutable int bands_per_batch = 0;    // counters per batch element: coarse bands, with the last one replaced by fine_bands
+  mutable int fine_bands = 0;         // 0: all bands are band_rows high; n: the last band_rows are n bands of fine_rows
+  mutable int fine_rows = 0;
+  mutable int signals_per_fine_band = 0;
 };
 
 int gemm_impl(const void* A, const void* B, void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,

@@ -97,6 +97,10 @@ struct GemmParams {
   int* band_counter;
   int band_tiles;       // tile rows per band
   int bands_per_batch;
+  // Tile rows from fine_from on form bands (and raster groups) of ONE tile row each: the last coarse band of a fused
+  // all_reduce is split so that the reduction left over when the GEMM ends is a quarter of a band, not a whole one.
+  // fine_from == m_tiles: off.  A multiple of band_tiles (and of group_m).
+  int fine_from;
   // Optional trace buffer (tools only; null in production), rows of 256 uint64 indexed by SM id:
   // row 0 = 1 + first tile index, row 1 + i = global-timer value at which the producer started
   // this CTA's i-th tile.
@@ -240,6 +244,12 @@ __device__ __forceinline__ void decode_tile(const GemmParams& p, int tile, int& 
   const int per_batch = p.m_tiles * p.n_tiles;
   b = tile / per_batch;
   const int r = tile - b * per_batch;
+  if (r >= p.fine_from * p.n_tiles) {  // the fine tail: one tile row after the other, left to right
+    const int rr = r - p.fine_from * p.n_tiles;
+    m_blk = p.fine_from + rr / p.n_tiles;
+    n_blk = rr - (m_blk - p.fine_from) * p.n_tiles;
+    return;
+  }
   const int span = p.group_m * p.n_tiles;
   const int g = r / span;
   const int first_m = g * p.group_m;
@@ -622,7 +632,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (lane == 0) {
         tma_store_wait<0>();  // the bulk stores have been performed, not merely read out of smem
         __threadfence();
-        int* ctr = p.band_counter + (size_t)b * p.bands_per_batch + m_blk / p.band_tiles;
+        const int band = m_blk < p.fine_from ? m_blk / p.band_tiles : p.fine_from / p.band_tiles + (m_blk - p.fine_from);
+        int* ctr = p.band_counter + (size_t)b * p.bands_per_batch + band;
         asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(ctr) : "memory");
       }
       __syncwarp();

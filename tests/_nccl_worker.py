@@ -101,6 +101,14 @@ def main(out_path):
         comm.bmm_allreduce_fused(Ab, Bb, shC, 2)
     torch.cuda.synchronize()
     res["fused_allreduce"] = oracle.reduced_sum_err(shC.local, terms, 1.0) <= TOL[torch.bfloat16]  # fp32 adds, ONE rounding to nearest
+    # the same with the last row band split into one-tile-row bands (B2MM_FINE_TAIL=1): other band geometry, same sums
+    coarse = shC.local.clone()
+    os.environ["B2MM_FINE_TAIL"] = "1"
+    for _ in range(2):
+        comm.bmm_allreduce_fused(Ab, Bb, shC, 2)
+    torch.cuda.synchronize()
+    os.environ.pop("B2MM_FINE_TAIL")
+    res["fused_allreduce_fine_tail_same_bits"] = bool(torch.equal(shC.local, coarse))
     Cn = b2.bmm(Ab, Bb)
     comm.all_reduce(Cn)
     torch.cuda.synchronize()
